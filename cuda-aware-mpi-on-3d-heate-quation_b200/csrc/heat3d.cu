@@ -1,0 +1,993 @@
+// libheat3d: C-ABI implementation (include/heat3d.h).  Host side of the heat3D hot path on B200:
+// slab bookkeeping, pitched double-buffered fields, TMA descriptors, streams/events, the step loop with
+// ghost-plane exchange overlapped with interior compute, fused residual, error norm, snapshots.
+//
+// There is no CPU path in this file: every entry point needs a CUDA device and says so when there is none.
+#include "../../include/heat3d.h"
+#include "kernels.cuh"
+
+#include <cfloat>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <dlfcn.h>
+#include <new>
+#include <vector>
+
+namespace {
+
+constexpr uint32_t HALO_RING = 256;
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CU_TRY(expr)                                                                                    \
+    do {                                                                                                \
+        cudaError_t e__ = (expr);                                                                       \
+        if (e__ != cudaSuccess)                                                                         \
+            return fail(HEAT3D_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+// ---- NCCL, bound at run time so the library loads (and single-process runs work) without it ------------
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+enum { ncclSuccess = 0 };
+enum { ncclFloat64 = 8 };
+enum { ncclMax = 2, ncclSum = 0 };
+struct NcclApi {
+    void* handle = nullptr;
+    int (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+} g_nccl;
+
+int load_nccl()
+{
+    if (g_nccl.handle) return HEAT3D_OK;
+    // If the host process already mapped a libnccl.so.2 (e.g. torch's bundled one) this returns that copy.
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!h) return fail(HEAT3D_ERR_NCCL, "cannot load libnccl.so.2: %s", dlerror());
+#define H3_SYM(field, name)                                                                  \
+    *(void**)(&g_nccl.field) = dlsym(h, name);                                               \
+    if (!g_nccl.field) return fail(HEAT3D_ERR_NCCL, "libnccl lacks symbol %s", name);
+    H3_SYM(GetUniqueId, "ncclGetUniqueId")
+    H3_SYM(CommInitRank, "ncclCommInitRank")
+    H3_SYM(CommDestroy, "ncclCommDestroy")
+    H3_SYM(Send, "ncclSend")
+    H3_SYM(Recv, "ncclRecv")
+    H3_SYM(AllReduce, "ncclAllReduce")
+    H3_SYM(GroupStart, "ncclGroupStart")
+    H3_SYM(GroupEnd, "ncclGroupEnd")
+    H3_SYM(GetErrorString, "ncclGetErrorString")
+#undef H3_SYM
+    g_nccl.handle = h;
+    return HEAT3D_OK;
+}
+
+#define NCCL_TRY(expr)                                                                                  \
+    do {                                                                                                \
+        int r__ = (expr);                                                                               \
+        if (r__ != ncclSuccess)                                                                         \
+            return fail(HEAT3D_ERR_NCCL, "%s failed: %s (%s:%d)", #expr, g_nccl.GetErrorString(r__), __FILE__, __LINE__); \
+    } while (0)
+
+// ---- cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda) -----------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode = nullptr;
+
+int load_encode()
+{
+    if (g_encode) return HEAT3D_OK;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    CU_TRY(cudaGetDriverEntryPointByVersion("cuTensorMapEncodeTiled", &fn, 12000, cudaEnableDefault, &q));
+    if (q != cudaDriverEntryPointSuccess || !fn) return fail(HEAT3D_ERR_CUDA, "driver lacks cuTensorMapEncodeTiled");
+    g_encode = (EncodeTiledFn)fn;
+    return HEAT3D_OK;
+}
+
+// ---- TMA kernel variants --------------------------------------------------------------------------------
+struct TmaVariant {
+    const char* name;
+    int tx, ty, ry, stages, minb;
+    size_t smem;
+    int threads;
+    const void* fn[2][2];   // [arith][res]
+};
+
+template <int TX, int TY, int RY, int ST, int MINB>
+TmaVariant make_variant(const char* name)
+{
+    TmaVariant v;
+    v.name = name;
+    v.tx = TX; v.ty = TY; v.ry = RY; v.stages = ST; v.minb = MINB;
+    v.smem = h3::TmaCfg<TX, TY, ST>::SMEM_BYTES;
+    v.threads = (TX / 2) * (TY / RY) + 32;
+    v.fn[0][0] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_STRICT, false, MINB>;
+    v.fn[0][1] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_STRICT, true, MINB>;
+    v.fn[1][0] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_FMA, false, MINB>;
+    v.fn[1][1] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_FMA, true, MINB>;
+    return v;
+}
+
+// tile_x, tile_y, rows/thread, stages, CTAs/SM.  First entry = default; others are selectable via params.tune.
+const std::vector<TmaVariant>& variants()
+{
+    static const std::vector<TmaVariant> v = {
+        make_variant<128, 32, 4, 4, 1>("tma_128x32_r4_s4_c1"),
+        make_variant<128, 32, 4, 5, 1>("tma_128x32_r4_s5_c1"),
+        make_variant<128, 32, 2, 4, 1>("tma_128x32_r2_s4_c1"),
+        make_variant<128, 16, 4, 4, 2>("tma_128x16_r4_s4_c2"),
+        make_variant<128, 16, 2, 4, 2>("tma_128x16_r2_s4_c2"),
+        make_variant<128, 16, 2, 5, 2>("tma_128x16_r2_s5_c2"),
+        make_variant<128, 8, 2, 4, 4>("tma_128x8_r2_s4_c4"),
+        make_variant<128, 8, 1, 6, 3>("tma_128x8_r1_s6_c3"),
+        make_variant<64, 32, 4, 4, 2>("tma_64x32_r4_s4_c2"),
+        make_variant<64, 16, 2, 4, 4>("tma_64x16_r2_s4_c4"),
+        make_variant<64, 8, 2, 4, 4>("tma_64x8_r2_s4_c4"),
+    };
+    return v;
+}
+
+struct Slab {
+    int dev = 0;
+    int gidx = 0;                 // global slab index
+    uint32_t z0 = 0, z1 = 0;      // owned global planes [z0, z1)
+    uint32_t G = 1;               // ghost depth
+    uint32_t planes = 0;          // allocated planes = (z1-z0) + 2G
+    long long zg0 = 0;            // global z of local plane 0 (= z0 - G)
+    uint32_t pitch = 0;
+    long long plane = 0;          // doubles per plane
+    double* buf[2] = {nullptr, nullptr};
+    CUtensorMap tmap[2];
+    cudaStream_t compute = nullptr, comm = nullptr, copy = nullptr;
+    bool own_compute = true;
+    cudaEvent_t ev_boundary = nullptr, ev_put = nullptr, ev_start = nullptr, ev_stop = nullptr, ev_snap = nullptr,
+                ev_tmp = nullptr;
+    std::vector<cudaEvent_t> ev_wait0, ev_wait1;   // HEAT3D_FLAG_TIME_HALO: brackets of the ghost wait, ring of HALO_RING steps
+    unsigned long long* d_res = nullptr;   // residual slot (bit pattern of a non-negative double)
+    double* d_partial = nullptr;           // error-norm scratch: partial sums
+    double* d_scalar = nullptr;            // error-norm result / allreduce staging
+    double* h_scalar = nullptr;            // pinned: 2 doubles
+    int partial_blocks = 0;
+    int num_sms = 0;
+    ncclComm_t nccl = nullptr;
+    bool lower = false, upper = false;     // has a neighbouring slab below / above
+    int za = 0, zb = 0;                    // local output plane range (owned ∩ global interior)
+};
+
+}  // namespace
+
+struct heat3d_ctx {
+    heat3d_params p;
+    std::vector<int32_t> devices;
+    std::vector<Slab> slabs;
+    int cur = 0;                       // buffer holding the current time level
+    const TmaVariant* variant = nullptr;
+    bool use_tma = true;
+    bool multi_process = false;
+    int snap_buf = -1;                 // buffer an async snapshot is still reading, or -1
+    bool have_res = false;
+    double last_res = 0.0;
+    heat3d_timing tm;
+    bool halo_timed = false;
+    bool timing_pending = false;       // a call's ev_start/ev_stop have not been folded into tm yet
+    uint32_t call_steps = 0;           // steps issued by the current/last call
+};
+
+namespace {
+
+int set_dev(const Slab& s)
+{
+    CU_TRY(cudaSetDevice(s.dev));
+    return HEAT3D_OK;
+}
+
+int make_tmap(Slab& s, int which, const heat3d_ctx* c)
+{
+    const TmaVariant& v = *c->variant;
+    cuuint64_t dims[3] = {c->p.nx, c->p.ny, s.planes};
+    cuuint64_t strides[2] = {(cuuint64_t)s.pitch * 8, (cuuint64_t)s.plane * 8};
+    cuuint32_t box[3] = {(cuuint32_t)(v.tx + 4), (cuuint32_t)(v.ty + 2), 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = g_encode(&s.tmap[which], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, s.buf[which], dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return HEAT3D_OK;
+}
+
+// One stencil launch over local output planes [za, zb) of slab s, reading buffer `src`.
+int launch_stencil(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res)
+{
+    if (zb <= za) return HEAT3D_OK;
+    h3::Geom g;
+    g.nx = (int)c->p.nx; g.ny = (int)c->p.ny; g.pitch = (int)s.pitch; g.plane = s.plane;
+    g.za = za; g.zb = zb; g.Dx = c->p.Dx; g.Dy = c->p.Dy; g.Dz = c->p.Dz;
+    const int ar = c->p.arith == HEAT3D_ARITH_FMA ? 1 : 0;
+    double* dst = s.buf[src ^ 1];
+    if (c->use_tma) {
+        const TmaVariant& v = *c->variant;
+        h3::TmaWork w;
+        w.ntx = ((int)c->p.nx + v.tx - 1) / v.tx;
+        w.nty = ((int)c->p.ny + v.ty - 1) / v.ty;
+        w.total = (long long)w.ntx * w.nty * (zb - za);
+        long long grid = (long long)s.num_sms * v.minb;
+        if (grid > w.total) grid = w.total;
+        w.per_cta = (w.total + grid - 1) / grid;
+        grid = (w.total + w.per_cta - 1) / w.per_cta;
+        void* args[] = {(void*)&s.tmap[src], (void*)&dst, (void*)&g, (void*)&w, (void*)&s.d_res};
+        CU_TRY(cudaLaunchKernel(v.fn[ar][res ? 1 : 0], dim3((unsigned)grid), dim3(v.threads), args, v.smem, s.compute));
+    } else {
+        const dim3 block(64, 4);
+        const int nzp = zb - za;
+        const int xy_blocks = ((g.nx + 63) / 64) * ((g.ny + 3) / 4);
+        int chunks = (4 * s.num_sms * 8 + xy_blocks - 1) / xy_blocks;      // aim for ~4 waves of 8 CTAs/SM
+        if (chunks > nzp) chunks = nzp;
+        if (chunks < 1) chunks = 1;
+        const int zchunk = (nzp + chunks - 1) / chunks;
+        const dim3 grid((g.nx + 63) / 64, (g.ny + 3) / 4, (nzp + zchunk - 1) / zchunk);
+        const double* srcp = s.buf[src];
+#define H3_LAUNCH_BASE(A, R) h3::stencil_baseline_kernel<A, R><<<grid, block, 0, s.compute>>>(srcp, dst, g, zchunk, s.d_res)
+        if (ar == 0 && !res) H3_LAUNCH_BASE(h3::ARITH_STRICT, false);
+        else if (ar == 0 && res) H3_LAUNCH_BASE(h3::ARITH_STRICT, true);
+        else if (ar == 1 && !res) H3_LAUNCH_BASE(h3::ARITH_FMA, false);
+        else H3_LAUNCH_BASE(h3::ARITH_FMA, true);
+#undef H3_LAUNCH_BASE
+        CU_TRY(cudaGetLastError());
+    }
+    c->tm.launches++;
+    c->tm.last_call_launches++;
+    c->tm.last_call_stencil_launches++;
+    return HEAT3D_OK;
+}
+
+Slab* local_slab(heat3d_ctx* c, int gidx)
+{
+    const int i = gidx - c->p.slab_first;
+    return (i >= 0 && i < (int)c->slabs.size()) ? &c->slabs[i] : nullptr;
+}
+
+// Push the outermost G owned planes of buffer `b` into the neighbours' ghost planes of their buffer `b`
+// (same-process neighbours: peer copy; other processes: NCCL send/recv), on each slab's comm stream,
+// after that slab's ev_boundary.  Records ev_put per slab.
+int exchange_ghosts(heat3d_ctx* c, int b)
+{
+    bool any_nccl = false;
+    for (Slab& s : c->slabs) {
+        if (!s.lower && !s.upper) continue;
+        int rc = set_dev(s);
+        if (rc) return rc;
+        CU_TRY(cudaStreamWaitEvent(s.comm, s.ev_boundary, 0));
+        const size_t bytes = (size_t)s.G * s.plane * sizeof(double);
+        const uint32_t nzl = s.z1 - s.z0;
+        if (s.lower) {
+            if (Slab* n = local_slab(c, s.gidx - 1)) {   // my first G owned planes -> n's upper ghost
+                const double* from = s.buf[b] + (long long)s.G * s.plane;
+                double* to = n->buf[b] + (long long)(n->G + (n->z1 - n->z0)) * n->plane;
+                CU_TRY(cudaMemcpyPeerAsync(to, n->dev, from, s.dev, bytes, s.comm));
+            } else any_nccl = true;
+        }
+        if (s.upper) {
+            if (Slab* n = local_slab(c, s.gidx + 1)) {   // my last G owned planes -> n's lower ghost
+                const double* from = s.buf[b] + (long long)nzl * s.plane;
+                double* to = n->buf[b];
+                CU_TRY(cudaMemcpyPeerAsync(to, n->dev, from, s.dev, bytes, s.comm));
+            } else any_nccl = true;
+        }
+    }
+    if (any_nccl) {
+        NCCL_TRY(g_nccl.GroupStart());
+        for (Slab& s : c->slabs) {
+            const size_t cnt = (size_t)s.G * s.plane;
+            const uint32_t nzl = s.z1 - s.z0;
+            if (s.lower && !local_slab(c, s.gidx - 1)) {
+                NCCL_TRY(g_nccl.Send(s.buf[b] + (long long)s.G * s.plane, cnt, ncclFloat64, s.gidx - 1, s.nccl, s.comm));
+                NCCL_TRY(g_nccl.Recv(s.buf[b], cnt, ncclFloat64, s.gidx - 1, s.nccl, s.comm));
+            }
+            if (s.upper && !local_slab(c, s.gidx + 1)) {
+                NCCL_TRY(g_nccl.Send(s.buf[b] + (long long)nzl * s.plane, cnt, ncclFloat64, s.gidx + 1, s.nccl, s.comm));
+                NCCL_TRY(g_nccl.Recv(s.buf[b] + (long long)(s.G + nzl) * s.plane, cnt, ncclFloat64, s.gidx + 1, s.nccl, s.comm));
+            }
+        }
+        NCCL_TRY(g_nccl.GroupEnd());
+    }
+    for (Slab& s : c->slabs) {
+        if (!s.lower && !s.upper) continue;
+        int rc = set_dev(s);
+        if (rc) return rc;
+        CU_TRY(cudaEventRecord(s.ev_put, s.comm));
+    }
+    return HEAT3D_OK;
+}
+
+// Make slab s's compute stream wait until its ghost planes (filled by the previous exchange) have landed.
+int wait_ghosts(heat3d_ctx* c, Slab& s)
+{
+    if (s.lower) {
+        Slab* n = local_slab(c, s.gidx - 1);
+        CU_TRY(cudaStreamWaitEvent(s.compute, n ? n->ev_put : s.ev_put, 0));
+    }
+    if (s.upper) {
+        Slab* n = local_slab(c, s.gidx + 1);
+        CU_TRY(cudaStreamWaitEvent(s.compute, n ? n->ev_put : s.ev_put, 0));
+    }
+    return HEAT3D_OK;
+}
+
+int step_once(heat3d_ctx* c, bool res)
+{
+    const int src = c->cur, dst = c->cur ^ 1;
+    const bool overlap = !(c->p.flags & HEAT3D_FLAG_NO_OVERLAP);
+    for (Slab& s : c->slabs) {
+        int rc = set_dev(s);
+        if (rc) return rc;
+        if (c->snap_buf == dst) CU_TRY(cudaStreamWaitEvent(s.compute, s.ev_snap, 0));
+        if (res) CU_TRY(cudaMemsetAsync(s.d_res, 0, sizeof(unsigned long long), s.compute));
+        if (!s.lower && !s.upper) {
+            if ((rc = launch_stencil(c, s, src, s.za, s.zb, res))) return rc;
+            continue;
+        }
+        if (c->halo_timed) CU_TRY(cudaEventRecord(s.ev_wait0[c->call_steps % HALO_RING], s.compute));
+        if ((rc = wait_ghosts(c, s))) return rc;
+        if (c->halo_timed) CU_TRY(cudaEventRecord(s.ev_wait1[c->call_steps % HALO_RING], s.compute));
+        // planes whose results the neighbours need first, then the rest while the exchange is in flight
+        const int G = (int)s.G;
+        int lo_end = s.lower ? s.za + G : s.za;
+        int hi_beg = s.upper ? s.zb - G : s.zb;
+        if (lo_end > s.zb) lo_end = s.zb;
+        if (hi_beg < lo_end) hi_beg = lo_end;
+        if (!overlap) { lo_end = s.za; hi_beg = s.zb; }
+        if ((rc = launch_stencil(c, s, src, s.za, lo_end, res))) return rc;
+        if ((rc = launch_stencil(c, s, src, hi_beg, s.zb, res))) return rc;
+        if (overlap) CU_TRY(cudaEventRecord(s.ev_boundary, s.compute));
+        if ((rc = launch_stencil(c, s, src, lo_end, hi_beg, res))) return rc;
+        if (!overlap) CU_TRY(cudaEventRecord(s.ev_boundary, s.compute));
+    }
+    if (c->snap_buf == dst) c->snap_buf = -1;
+    if (c->slabs.size() > 1 || c->multi_process) {
+        int rc = exchange_ghosts(c, dst);
+        if (rc) return rc;
+    }
+    c->cur = dst;
+    c->tm.steps++;
+    c->call_steps++;
+    return HEAT3D_OK;
+}
+
+int finish_timing(heat3d_ctx* c);
+
+int begin_call(heat3d_ctx* c)
+{
+    c->timing_pending = false;         // an unread previous call is dropped from total_ms, never waited for here
+    c->call_steps = 0;
+    c->tm.last_call_launches = 0;
+    c->tm.last_call_stencil_launches = 0;
+    for (Slab& s : c->slabs) {
+        int rc = set_dev(s);
+        if (rc) return rc;
+        CU_TRY(cudaEventRecord(s.ev_start, s.compute));
+    }
+    return HEAT3D_OK;
+}
+
+int end_call(heat3d_ctx* c)
+{
+    for (Slab& s : c->slabs) {
+        int rc = set_dev(s);
+        if (rc) return rc;
+        CU_TRY(cudaEventRecord(s.ev_stop, s.compute));
+    }
+    c->timing_pending = true;
+    return HEAT3D_OK;
+}
+
+// Device-side residual of the last step -> host double (max over local slabs and, with NCCL, processes).
+int fetch_residual(heat3d_ctx* c, double* out)
+{
+    double r = 0.0;
+    for (Slab& s : c->slabs) {
+        int rc = set_dev(s);
+        if (rc) return rc;
+        if (c->multi_process) {
+            // bit patterns of non-negative doubles order like the doubles: reduce as fp64 max.
+            CU_TRY(cudaStreamWaitEvent(s.comm, s.ev_stop, 0));
+            NCCL_TRY(g_nccl.AllReduce(s.d_res, s.d_scalar, 1, ncclFloat64, ncclMax, s.nccl, s.comm));
+            CU_TRY(cudaMemcpyAsync(s.h_scalar, s.d_scalar, sizeof(double), cudaMemcpyDeviceToHost, s.comm));
+            CU_TRY(cudaStreamSynchronize(s.comm));
+        } else {
+            CU_TRY(cudaMemcpyAsync(s.h_scalar, s.d_res, sizeof(double), cudaMemcpyDeviceToHost, s.compute));
+            CU_TRY(cudaStreamSynchronize(s.compute));
+        }
+        if (s.h_scalar[0] > r) r = s.h_scalar[0];
+    }
+    if (r < DBL_MIN) r = DBL_MIN;     // reference starts its max at numeric_limits<double>::min() (cu:1019)
+    *out = r;
+    c->have_res = true;
+    c->last_res = r;
+    return HEAT3D_OK;
+}
+
+int finish_timing(heat3d_ctx* c)
+{
+    if (!c->timing_pending) return HEAT3D_OK;
+    double worst = 0.0, halo = 0.0;
+    for (Slab& s : c->slabs) {
+        int rc = set_dev(s);
+        if (rc) return rc;
+        CU_TRY(cudaEventSynchronize(s.ev_stop));
+        float ms = 0.f;
+        CU_TRY(cudaEventElapsedTime(&ms, s.ev_start, s.ev_stop));
+        if (ms > worst) worst = ms;
+        if (c->halo_timed && (s.lower || s.upper) && c->call_steps) {
+            const uint32_t n = c->call_steps < HALO_RING ? c->call_steps : HALO_RING;
+            double sum = 0.0;
+            for (uint32_t i = 0; i < n; ++i) {
+                float w = 0.f;
+                CU_TRY(cudaEventElapsedTime(&w, s.ev_wait0[i], s.ev_wait1[i]));
+                sum += w;
+            }
+            const double est = sum / n * c->call_steps;    // ring average scaled to the whole call
+            if (est > halo) halo = est;
+        }
+    }
+    c->tm.last_call_ms = worst;
+    c->tm.total_ms += worst;
+    c->tm.exposed_halo_ms = halo;
+    c->timing_pending = false;
+    return HEAT3D_OK;
+}
+
+void destroy_slab(Slab& s)
+{
+    cudaSetDevice(s.dev);
+    if (s.nccl && g_nccl.CommDestroy) g_nccl.CommDestroy(s.nccl);
+    for (int b = 0; b < 2; ++b)
+        if (s.buf[b]) cudaFree(s.buf[b]);
+    if (s.d_res) cudaFree(s.d_res);
+    if (s.d_partial) cudaFree(s.d_partial);
+    if (s.d_scalar) cudaFree(s.d_scalar);
+    if (s.h_scalar) cudaFreeHost(s.h_scalar);
+    cudaEvent_t* evs[] = {&s.ev_boundary, &s.ev_put, &s.ev_start, &s.ev_stop, &s.ev_snap, &s.ev_tmp};
+    for (cudaEvent_t* e : evs)
+        if (*e) cudaEventDestroy(*e);
+    for (cudaEvent_t e : s.ev_wait0) cudaEventDestroy(e);
+    for (cudaEvent_t e : s.ev_wait1) cudaEventDestroy(e);
+    if (s.compute && s.own_compute) cudaStreamDestroy(s.compute);
+    if (s.comm) cudaStreamDestroy(s.comm);
+    if (s.copy) cudaStreamDestroy(s.copy);
+}
+
+int setup_slab(heat3d_ctx* c, Slab& s)
+{
+    int rc = set_dev(s);
+    if (rc) return rc;
+    cudaDeviceProp prop;
+    CU_TRY(cudaGetDeviceProperties(&prop, s.dev));
+    if (prop.major < 10)
+        return fail(HEAT3D_ERR_CUDA, "device %d is sm_%d%d; libheat3d is built for sm_100a (B200) only", s.dev, prop.major, prop.minor);
+    s.num_sms = prop.multiProcessorCount;
+    const heat3d_params& p = c->p;
+    s.pitch = (p.nx + 15u) / 16u * 16u;
+    s.plane = (long long)s.pitch * p.ny;
+    s.planes = (s.z1 - s.z0) + 2 * s.G;
+    s.zg0 = (long long)s.z0 - s.G;
+    const size_t bytes = (size_t)s.planes * s.plane * sizeof(double);
+    for (int b = 0; b < 2; ++b) {
+        cudaError_t e = cudaMalloc(&s.buf[b], bytes);
+        if (e != cudaSuccess) return fail(HEAT3D_ERR_ALLOC, "cudaMalloc of %zu bytes on device %d failed: %s", bytes, s.dev, cudaGetErrorString(e));
+        CU_TRY(cudaMemset(s.buf[b], 0, bytes));
+    }
+    if (p.stream && c->slabs.size() == 1) { s.compute = (cudaStream_t)p.stream; s.own_compute = false; }
+    else CU_TRY(cudaStreamCreateWithFlags(&s.compute, cudaStreamNonBlocking));
+    CU_TRY(cudaStreamCreateWithFlags(&s.comm, cudaStreamNonBlocking));
+    CU_TRY(cudaStreamCreateWithFlags(&s.copy, cudaStreamNonBlocking));
+    cudaEvent_t* sync_evs[] = {&s.ev_boundary, &s.ev_put, &s.ev_snap, &s.ev_tmp};
+    for (cudaEvent_t* e : sync_evs) CU_TRY(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    cudaEvent_t* time_evs[] = {&s.ev_start, &s.ev_stop};
+    for (cudaEvent_t* e : time_evs) CU_TRY(cudaEventCreate(e));
+    if (c->halo_timed) {
+        s.ev_wait0.resize(HALO_RING);
+        s.ev_wait1.resize(HALO_RING);
+        for (uint32_t i = 0; i < HALO_RING; ++i) {
+            CU_TRY(cudaEventCreate(&s.ev_wait0[i]));
+            CU_TRY(cudaEventCreate(&s.ev_wait1[i]));
+        }
+    }
+    CU_TRY(cudaMalloc(&s.d_res, sizeof(unsigned long long)));
+    CU_TRY(cudaMemset(s.d_res, 0, sizeof(unsigned long long)));
+    s.partial_blocks = s.num_sms * 8;
+    CU_TRY(cudaMalloc(&s.d_partial, (size_t)s.partial_blocks * sizeof(double)));
+    CU_TRY(cudaMalloc(&s.d_scalar, 2 * sizeof(double)));
+    CU_TRY(cudaHostAlloc(&s.h_scalar, 2 * sizeof(double), cudaHostAllocDefault));
+    // local output range: owned planes that are global interior planes
+    long long a = (long long)s.G, b = (long long)s.G + (s.z1 - s.z0);
+    const long long lo = 1 - s.zg0, hi = (long long)p.nz - 1 - s.zg0;
+    if (a < lo) a = lo;
+    if (b > hi) b = hi;
+    if (b < a) b = a;
+    s.za = (int)a;
+    s.zb = (int)b;
+    s.lower = s.gidx > 0;
+    s.upper = s.gidx < p.nslabs - 1;
+    if (c->use_tma) {
+        for (int w = 0; w < 2; ++w)
+            if ((rc = make_tmap(s, w, c))) return rc;
+        const TmaVariant& v = *c->variant;
+        for (int ar = 0; ar < 2; ++ar)
+            for (int r = 0; r < 2; ++r)
+                CU_TRY(cudaFuncSetAttribute(v.fn[ar][r], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v.smem));
+    }
+    return HEAT3D_OK;
+}
+
+int check_ctx(const heat3d_ctx* c)
+{
+    if (!c) return fail(HEAT3D_ERR_INVALID, "null context");
+    return HEAT3D_OK;
+}
+
+// rows of nx doubles: host dense <-> device pitched, planes [zl, zl+n) of slab s buffer b
+int copy_planes(Slab& s, int b, uint32_t nx, uint32_t ny, uint32_t zl, uint32_t n, double* host, bool to_device, cudaStream_t st)
+{
+    double* dev = s.buf[b] + (long long)zl * s.plane;
+    const size_t rows = (size_t)ny * n;
+    if (s.pitch == nx) {   // rows are dense on the device too: one flat copy
+        if (to_device) CU_TRY(cudaMemcpyAsync(dev, host, rows * nx * 8, cudaMemcpyHostToDevice, st));
+        else CU_TRY(cudaMemcpyAsync(host, dev, rows * nx * 8, cudaMemcpyDeviceToHost, st));
+        return HEAT3D_OK;
+    }
+    if (to_device)
+        CU_TRY(cudaMemcpy2DAsync(dev, (size_t)s.pitch * 8, host, (size_t)nx * 8, (size_t)nx * 8, rows, cudaMemcpyHostToDevice, st));
+    else
+        CU_TRY(cudaMemcpy2DAsync(host, (size_t)nx * 8, dev, (size_t)s.pitch * 8, (size_t)nx * 8, rows, cudaMemcpyDeviceToHost, st));
+    return HEAT3D_OK;
+}
+
+}  // namespace
+
+// =========================================================================================================
+extern "C" {
+
+const char* heat3d_last_error(void) { return g_err; }
+int heat3d_version(void) { return HEAT3D_VERSION; }
+
+void heat3d_default_params(heat3d_params* p, uint32_t nx, uint32_t ny, uint32_t nz)
+{
+    memset(p, 0, sizeof *p);
+    p->struct_size = (uint32_t)sizeof *p;
+    p->nx = nx; p->ny = ny; p->nz = nz;
+    p->arith = HEAT3D_ARITH_STRICT;
+    p->temporal_k = 1;
+    p->kernel = HEAT3D_KERNEL_AUTO;
+    p->nslabs = 1; p->slab_first = 0; p->nlocal = 1;
+}
+
+int heat3d_nccl_unique_id(void* out128)
+{
+    if (!out128) return fail(HEAT3D_ERR_INVALID, "null output");
+    int rc = load_nccl();
+    if (rc) return rc;
+    ncclUniqueId id;
+    NCCL_TRY(g_nccl.GetUniqueId(&id));
+    memcpy(out128, &id, sizeof id);
+    return HEAT3D_OK;
+}
+
+int heat3d_create(const heat3d_params* pin, heat3d_ctx** out)
+{
+    if (!pin || !out) return fail(HEAT3D_ERR_INVALID, "null argument");
+    *out = nullptr;
+    if (pin->struct_size != sizeof(heat3d_params))
+        return fail(HEAT3D_ERR_INVALID, "heat3d_params.struct_size %u != %zu (header/library mismatch)", pin->struct_size, sizeof(heat3d_params));
+    heat3d_params p = *pin;
+    if (p.nx < 3 || p.ny < 3 || p.nz < 3) return fail(HEAT3D_ERR_INVALID, "grid %ux%ux%u: every axis needs >= 3 points", p.nx, p.ny, p.nz);
+    if (p.nx > (1u << 30) || p.ny > (1u << 30) || p.nz > (1u << 30)) return fail(HEAT3D_ERR_INVALID, "grid axis too large");
+    if (p.arith != HEAT3D_ARITH_STRICT && p.arith != HEAT3D_ARITH_FMA) return fail(HEAT3D_ERR_INVALID, "unknown arith %d", p.arith);
+    if (p.temporal_k <= 0) p.temporal_k = 1;
+    if (p.temporal_k != 1) return fail(HEAT3D_ERR_INVALID, "temporal_k=%d not available in this build (only 1)", p.temporal_k);
+    if (p.nslabs <= 0) p.nslabs = 1;
+    if (p.nlocal <= 0) p.nlocal = p.nslabs;
+    if (p.slab_first < 0 || p.slab_first + p.nlocal > p.nslabs) return fail(HEAT3D_ERR_INVALID, "slab range [%d,%d) outside [0,%d)", p.slab_first, p.slab_first + p.nlocal, p.nslabs);
+    if ((uint32_t)p.nslabs > p.nz / (uint32_t)p.temporal_k) return fail(HEAT3D_ERR_INVALID, "%d slabs for %u planes: every slab needs >= %d planes", p.nslabs, p.nz, p.temporal_k);
+    const bool multi_process = p.nlocal < p.nslabs;
+    if (multi_process && !p.nccl_unique_id) return fail(HEAT3D_ERR_INVALID, "nccl_unique_id required when nlocal < nslabs");
+    if (multi_process && p.nlocal != 1) return fail(HEAT3D_ERR_INVALID, "a multi-process run takes one slab per process (nlocal=1), got %d", p.nlocal);
+
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(HEAT3D_ERR_CUDA, "no usable CUDA device (%s); libheat3d has no CPU fallback", e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+
+    heat3d_ctx* c = new (std::nothrow) heat3d_ctx();
+    if (!c) return fail(HEAT3D_ERR_ALLOC, "out of host memory");
+    c->p = p;
+    memset(&c->tm, 0, sizeof c->tm);
+    c->multi_process = multi_process;
+    c->halo_timed = (p.flags & HEAT3D_FLAG_TIME_HALO) != 0;
+    int cur_dev = 0;
+    cudaGetDevice(&cur_dev);
+    for (int i = 0; i < p.nlocal; ++i) c->devices.push_back(p.devices ? p.devices[i] : cur_dev);
+    c->p.devices = nullptr;
+    c->p.nccl_unique_id = nullptr;
+    for (int d : c->devices)
+        if (d < 0 || d >= ndev) { delete c; return fail(HEAT3D_ERR_INVALID, "device ordinal %d out of range [0,%d)", d, ndev); }
+
+    // kernel selection
+    c->use_tma = p.kernel != HEAT3D_KERNEL_BASELINE;
+    int rc = HEAT3D_OK;
+    if (c->use_tma) {
+        if ((rc = load_encode())) { delete c; return rc; }
+        const auto& vs = variants();
+        c->variant = &vs[0];
+        if (p.tune[0] || p.tune[1] || p.tune[2] || p.tune[3] || p.tune[4]) {
+            c->variant = nullptr;
+            for (const TmaVariant& v : vs)
+                if ((!p.tune[0] || p.tune[0] == v.tx) && (!p.tune[1] || p.tune[1] == v.ty) && (!p.tune[2] || p.tune[2] == v.ry) &&
+                    (!p.tune[3] || p.tune[3] == v.stages) && (!p.tune[4] || p.tune[4] == v.minb)) { c->variant = &v; break; }
+            if (!c->variant) { delete c; return fail(HEAT3D_ERR_INVALID, "no TMA kernel variant matches tune={%d,%d,%d,%d,%d}", p.tune[0], p.tune[1], p.tune[2], p.tune[3], p.tune[4]); }
+        }
+    }
+
+    c->slabs.resize(p.nlocal);
+    for (int i = 0; i < p.nlocal; ++i) {
+        Slab& s = c->slabs[i];
+        s.dev = c->devices[i];
+        s.gidx = p.slab_first + i;
+        s.z0 = (uint32_t)((uint64_t)s.gidx * p.nz / p.nslabs);
+        s.z1 = (uint32_t)((uint64_t)(s.gidx + 1) * p.nz / p.nslabs);
+        s.G = (uint32_t)p.temporal_k;
+    }
+    for (Slab& s : c->slabs)
+        if ((rc = setup_slab(c, s))) { heat3d_destroy(c); return rc; }
+
+    // peer access between distinct devices of this context
+    for (size_t i = 0; i + 1 < c->slabs.size(); ++i) {
+        const int a = c->slabs[i].dev, b = c->slabs[i + 1].dev;
+        if (a == b) continue;
+        int can = 0;
+        cudaDeviceCanAccessPeer(&can, a, b);
+        if (can) {
+            cudaSetDevice(a); cudaError_t e1 = cudaDeviceEnablePeerAccess(b, 0);
+            cudaSetDevice(b); cudaError_t e2 = cudaDeviceEnablePeerAccess(a, 0);
+            (void)e1; (void)e2;
+            cudaGetLastError();   // "already enabled" is fine
+        }
+    }
+    if (multi_process) {
+        if ((rc = load_nccl())) { heat3d_destroy(c); return rc; }
+        ncclUniqueId id;
+        memcpy(&id, p.nccl_unique_id, sizeof id);
+        int r = g_nccl.GroupStart();
+        for (Slab& s : c->slabs) {
+            cudaSetDevice(s.dev);
+            if (r == ncclSuccess) r = g_nccl.CommInitRank(&s.nccl, p.nslabs, id, s.gidx);
+        }
+        if (r == ncclSuccess) r = g_nccl.GroupEnd();
+        if (r != ncclSuccess) { fail(HEAT3D_ERR_NCCL, "ncclCommInitRank failed: %s", g_nccl.GetErrorString(r)); heat3d_destroy(c); return HEAT3D_ERR_NCCL; }
+    }
+    cudaSetDevice(c->slabs[0].dev);
+    *out = c;
+    return HEAT3D_OK;
+}
+
+int heat3d_destroy(heat3d_ctx* c)
+{
+    if (!c) return HEAT3D_OK;
+    for (Slab& s : c->slabs) {
+        cudaSetDevice(s.dev);
+        cudaDeviceSynchronize();
+    }
+    for (Slab& s : c->slabs) destroy_slab(s);
+    delete c;
+    return HEAT3D_OK;
+}
+
+int heat3d_local_range(const heat3d_ctx* c, uint32_t* z0, uint32_t* z1)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (z0) *z0 = c->slabs.front().z0;
+    if (z1) *z1 = c->slabs.back().z1;
+    return HEAT3D_OK;
+}
+
+int heat3d_layout(const heat3d_ctx* c, int32_t i, uint32_t* pitch, uint32_t* planes, uint32_t* ghost)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (i < 0 || i >= (int)c->slabs.size()) return fail(HEAT3D_ERR_INVALID, "local slab %d out of range", i);
+    if (pitch) *pitch = c->slabs[i].pitch;
+    if (planes) *planes = c->slabs[i].planes;
+    if (ghost) *ghost = c->slabs[i].G;
+    return HEAT3D_OK;
+}
+
+const char* heat3d_kernel_name(const heat3d_ctx* c)
+{
+    if (!c) return "";
+    return c->use_tma ? c->variant->name : "baseline_64x4";
+}
+
+void* heat3d_compute_stream(heat3d_ctx* c, int32_t i)
+{
+    if (!c || i < 0 || i >= (int)c->slabs.size()) return nullptr;
+    return (void*)c->slabs[i].compute;
+}
+
+int heat3d_sync(heat3d_ctx* c)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    for (Slab& s : c->slabs) {
+        if ((rc = set_dev(s))) return rc;
+        CU_TRY(cudaStreamSynchronize(s.compute));
+        CU_TRY(cudaStreamSynchronize(s.comm));
+        CU_TRY(cudaStreamSynchronize(s.copy));
+    }
+    return HEAT3D_OK;
+}
+
+int heat3d_init_reference_field(heat3d_ctx* c, double sp_y)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if ((rc = heat3d_sync(c))) return rc;
+    for (Slab& s : c->slabs) {
+        if ((rc = set_dev(s))) return rc;
+        h3::init_reference_field_kernel<<<s.num_sms * 8, 256, 0, s.compute>>>(s.buf[0], s.buf[1], (int)c->p.nx, (int)c->p.ny, (int)s.pitch,
+                                                                             (int)s.planes, s.zg0, (int)c->p.nz, sp_y);
+        CU_TRY(cudaGetLastError());
+        c->tm.launches++;
+        // ghosts are filled by the formula itself, so the first step has nothing to wait for
+        CU_TRY(cudaEventRecord(s.ev_put, s.compute));
+    }
+    c->cur = 0;
+    c->have_res = false;
+    return heat3d_sync(c);
+}
+
+int heat3d_upload_planes(heat3d_ctx* c, const double* host, uint32_t z0, uint32_t n)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (!host) return fail(HEAT3D_ERR_INVALID, "null host pointer");
+    if (z0 < c->slabs.front().z0 || z0 + n > c->slabs.back().z1)
+        return fail(HEAT3D_ERR_INVALID, "planes [%u,%u) outside this context's range [%u,%u)", z0, z0 + n, c->slabs.front().z0, c->slabs.back().z1);
+    if ((rc = heat3d_sync(c))) return rc;
+    const size_t plane_host = (size_t)c->p.nx * c->p.ny;
+    for (Slab& s : c->slabs) {
+        const uint32_t a = z0 > s.z0 ? z0 : s.z0, b = (z0 + n) < s.z1 ? (z0 + n) : s.z1;
+        if (b <= a) continue;
+        if ((rc = set_dev(s))) return rc;
+        const uint32_t zl = a - s.z0 + s.G;
+        for (int w = 0; w < 2; ++w)   // both buffers carry the Dirichlet shell
+            if ((rc = copy_planes(s, w, c->p.nx, c->p.ny, zl, b - a, const_cast<double*>(host) + (size_t)(a - z0) * plane_host, true, s.compute))) return rc;
+    }
+    // refresh ghost planes of both buffers from the neighbours
+    for (Slab& s : c->slabs) {
+        if ((rc = set_dev(s))) return rc;
+        CU_TRY(cudaEventRecord(s.ev_boundary, s.compute));
+    }
+    if (c->slabs.size() > 1 || c->multi_process)
+        for (int w = 0; w < 2; ++w)
+            if ((rc = exchange_ghosts(c, w))) return rc;
+    c->have_res = false;
+    return heat3d_sync(c);
+}
+
+int heat3d_upload(heat3d_ctx* c, const double* host_global)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (!host_global) return fail(HEAT3D_ERR_INVALID, "null host pointer");
+    const uint32_t z0 = c->slabs.front().z0, z1 = c->slabs.back().z1;
+    return heat3d_upload_planes(c, host_global + (size_t)z0 * c->p.nx * c->p.ny, z0, z1 - z0);
+}
+
+int heat3d_download_planes(heat3d_ctx* c, double* host, uint32_t z0, uint32_t n)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (!host) return fail(HEAT3D_ERR_INVALID, "null host pointer");
+    if (z0 < c->slabs.front().z0 || z0 + n > c->slabs.back().z1)
+        return fail(HEAT3D_ERR_INVALID, "planes [%u,%u) outside this context's range [%u,%u)", z0, z0 + n, c->slabs.front().z0, c->slabs.back().z1);
+    const size_t plane_host = (size_t)c->p.nx * c->p.ny;
+    for (Slab& s : c->slabs) {
+        const uint32_t a = z0 > s.z0 ? z0 : s.z0, b = (z0 + n) < s.z1 ? (z0 + n) : s.z1;
+        if (b <= a) continue;
+        if ((rc = set_dev(s))) return rc;
+        if ((rc = copy_planes(s, c->cur, c->p.nx, c->p.ny, a - s.z0 + s.G, b - a, host + (size_t)(a - z0) * plane_host, false, s.compute))) return rc;
+    }
+    return heat3d_sync(c);
+}
+
+int heat3d_download(heat3d_ctx* c, double* host_global)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (!host_global) return fail(HEAT3D_ERR_INVALID, "null host pointer");
+    const uint32_t z0 = c->slabs.front().z0, z1 = c->slabs.back().z1;
+    return heat3d_download_planes(c, host_global + (size_t)z0 * c->p.nx * c->p.ny, z0, z1 - z0);
+}
+
+int heat3d_step(heat3d_ctx* c, uint32_t nsteps)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if ((rc = begin_call(c))) return rc;
+    for (uint32_t i = 0; i < nsteps; ++i)
+        if ((rc = step_once(c, false))) return rc;
+    if (nsteps) c->have_res = false;
+    return end_call(c);
+}
+
+int heat3d_step_residual(heat3d_ctx* c, uint32_t nsteps, double* residual)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (!residual) return fail(HEAT3D_ERR_INVALID, "null residual pointer");
+    if (nsteps == 0) return fail(HEAT3D_ERR_INVALID, "nsteps must be >= 1 to produce a residual");
+    if ((rc = begin_call(c))) return rc;
+    for (uint32_t i = 0; i + 1 < nsteps; ++i)
+        if ((rc = step_once(c, false))) return rc;
+    if ((rc = step_once(c, true))) return rc;
+    if ((rc = end_call(c))) return rc;
+    return fetch_residual(c, residual);
+}
+
+int heat3d_residual(heat3d_ctx* c, double* residual)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (!residual) return fail(HEAT3D_ERR_INVALID, "null residual pointer");
+    if (!c->have_res) return fail(HEAT3D_ERR_STATE, "no residual recorded: the last update was not made by heat3d_step_residual/heat3d_run");
+    *residual = c->last_res;
+    return HEAT3D_OK;
+}
+
+int heat3d_run(heat3d_ctx* c, uint32_t iter_max, double eps, uint32_t check_every, uint32_t* final_iters, int32_t* converged,
+               uint32_t* applied)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (check_every == 0) check_every = 1;
+    double norm = 1.0;                 // cu:325
+    uint32_t fin = 0, done = 0;
+    int32_t conv = 0;
+    uint32_t time = 0;
+    while (time < iter_max) {
+        // next iteration index whose residual is examined: 0, then multiples of check_every (…-1), capped at the end
+        uint32_t target = time == 0 ? 0 : ((time / check_every) + 1) * check_every - 1;
+        if (target < time) target = time;
+        if (target > iter_max - 1) target = iter_max - 1;
+        double res = 0.0;
+        if ((rc = heat3d_step_residual(c, target - time + 1, &res))) return rc;
+        done += target - time + 1;
+        if (target == 0 && res != 0.0) norm = res;            // cu:1030-1032
+        if (res / norm < eps) { conv = 1; fin = target; break; }   // cu:1055-1073
+        time = target + 1;
+    }
+    if (final_iters) *final_iters = fin;
+    if (converged) *converged = conv;
+    if (applied) *applied = done;
+    return HEAT3D_OK;
+}
+
+int heat3d_mean_abs_error_vs_y(heat3d_ctx* c, double sp_y, double* err)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (!err) return fail(HEAT3D_ERR_INVALID, "null output pointer");
+    double sum = 0.0;
+    for (Slab& s : c->slabs) {
+        if ((rc = set_dev(s))) return rc;
+        if (s.zb > s.za) {
+            h3::abs_error_partial_kernel<<<s.partial_blocks, 256, 0, s.compute>>>(s.buf[c->cur], (int)c->p.nx, (int)c->p.ny, (int)s.pitch,
+                                                                                  s.plane, s.za, s.zb, sp_y, s.d_partial);
+            CU_TRY(cudaGetLastError());
+            h3::sum_partials_kernel<<<1, 256, 0, s.compute>>>(s.d_partial, s.partial_blocks, s.d_scalar);
+            CU_TRY(cudaGetLastError());
+            c->tm.launches += 2;
+        } else {
+            CU_TRY(cudaMemsetAsync(s.d_scalar, 0, sizeof(double), s.compute));
+        }
+        if (c->multi_process) {
+            CU_TRY(cudaEventRecord(s.ev_tmp, s.compute));
+            CU_TRY(cudaStreamWaitEvent(s.comm, s.ev_tmp, 0));
+            NCCL_TRY(g_nccl.AllReduce(s.d_scalar, s.d_scalar + 1, 1, ncclFloat64, ncclSum, s.nccl, s.comm));
+            CU_TRY(cudaMemcpyAsync(s.h_scalar, s.d_scalar + 1, sizeof(double), cudaMemcpyDeviceToHost, s.comm));
+            CU_TRY(cudaStreamSynchronize(s.comm));
+        } else {
+            CU_TRY(cudaMemcpyAsync(s.h_scalar, s.d_scalar, sizeof(double), cudaMemcpyDeviceToHost, s.compute));
+            CU_TRY(cudaStreamSynchronize(s.compute));
+        }
+        sum += s.h_scalar[0];
+        if (c->multi_process) break;   // the all-reduced value is already global
+    }
+    // the reference divides by an `unsigned` product (cu:1102); keep its wrap-around for grids beyond 2^32 cells
+    const unsigned denom = (c->p.nx - 2u) * (c->p.ny - 2u) * (c->p.nz - 2u);
+    *err = sum / denom;
+    return HEAT3D_OK;
+}
+
+int heat3d_snapshot_async(heat3d_ctx* c, double* pinned)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (!pinned) return fail(HEAT3D_ERR_INVALID, "null host pointer");
+    if (c->snap_buf >= 0 && (rc = heat3d_snapshot_wait(c))) return rc;
+    const size_t plane_host = (size_t)c->p.nx * c->p.ny;
+    for (Slab& s : c->slabs) {
+        if ((rc = set_dev(s))) return rc;
+        CU_TRY(cudaEventRecord(s.ev_tmp, s.compute));
+        CU_TRY(cudaStreamWaitEvent(s.copy, s.ev_tmp, 0));
+        if ((rc = copy_planes(s, c->cur, c->p.nx, c->p.ny, s.G, s.z1 - s.z0, pinned + (size_t)s.z0 * plane_host, false, s.copy))) return rc;
+        CU_TRY(cudaEventRecord(s.ev_snap, s.copy));
+    }
+    c->snap_buf = c->cur;
+    return HEAT3D_OK;
+}
+
+int heat3d_snapshot_wait(heat3d_ctx* c)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    for (Slab& s : c->slabs) {
+        if ((rc = set_dev(s))) return rc;
+        CU_TRY(cudaStreamSynchronize(s.copy));
+    }
+    c->snap_buf = -1;
+    return HEAT3D_OK;
+}
+
+int heat3d_host_alloc(void** out, size_t bytes)
+{
+    if (!out) return fail(HEAT3D_ERR_INVALID, "null output");
+    cudaError_t e = cudaHostAlloc(out, bytes, cudaHostAllocDefault);
+    if (e != cudaSuccess) return fail(HEAT3D_ERR_ALLOC, "cudaHostAlloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+    return HEAT3D_OK;
+}
+
+int heat3d_host_free(void* p)
+{
+    if (p) CU_TRY(cudaFreeHost(p));
+    return HEAT3D_OK;
+}
+
+int heat3d_get_timing(heat3d_ctx* c, heat3d_timing* t)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (!t) return fail(HEAT3D_ERR_INVALID, "null output");
+    if ((rc = finish_timing(c))) return rc;
+    *t = c->tm;
+    return HEAT3D_OK;
+}
+
+int heat3d_reset_timing(heat3d_ctx* c)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    memset(&c->tm, 0, sizeof c->tm);
+    return HEAT3D_OK;
+}
+
+}  // extern "C"

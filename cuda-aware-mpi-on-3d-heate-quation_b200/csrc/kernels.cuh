@@ -1,0 +1,376 @@
+// Device code of libheat3d: sm_100a kernels for the heat3D hot path.
+//
+// Field layout in HBM (one slab): planes[z_local][y][x], x fastest, row pitch `pitch` doubles
+// (multiple of 16 = 128 B), plane stride pitch*ny.  z_local 0 is global plane `zg0` (may be negative:
+// ghost planes of the first slab lie outside the domain and are never touched).
+//
+// Arithmetic of the update (reference HeatEquation3D/src/heat3D.cu:128-131):
+//   T' = T + Dx*(T[x+1] - 2T + T[x-1]) + Dy*(T[y+1] - 2T + T[y-1]) + Dz*(T[z+1] - 2T + T[z-1])
+// STRICT reproduces the host compiler's evaluation, one rounding per operation:
+//   s_d = (T[+1] - 2.0*T) + T[-1];   T' = ((T + Dx*s_x) + Dy*s_y) + Dz*s_z
+// FMA reproduces nvcc's contraction of the same source (PTX embedded in the reference's object file):
+//   c2 = T+T;  r = fma((T[x+1]-c2)+T[x-1], Dx, T);  r = fma(s_y, Dy, r);  r = fma(s_z, Dz, r)
+// Both are split as  partial_xy (needs only plane z)  +  finish_z (needs planes z-1, z+1)  so the
+// streaming kernels can touch each staged plane exactly once; the split does not change any rounding.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace h3 {
+
+enum { ARITH_STRICT = 0, ARITH_FMA = 1 };
+
+template <int ARITH>
+__device__ __forceinline__ double partial_xy(double c, double xm, double xp, double ym, double yp, double Dx, double Dy)
+{
+    if (ARITH == ARITH_STRICT) {
+        const double c2 = __dmul_rn(2.0, c);
+        const double sx = __dadd_rn(__dsub_rn(xp, c2), xm);
+        const double sy = __dadd_rn(__dsub_rn(yp, c2), ym);
+        return __dadd_rn(__dadd_rn(c, __dmul_rn(Dx, sx)), __dmul_rn(Dy, sy));
+    } else {
+        const double c2 = __dadd_rn(c, c);
+        const double sx = __dadd_rn(__dsub_rn(xp, c2), xm);
+        const double sy = __dadd_rn(__dsub_rn(yp, c2), ym);
+        return __fma_rn(sy, Dy, __fma_rn(sx, Dx, c));
+    }
+}
+
+template <int ARITH>
+__device__ __forceinline__ double finish_z(double t, double c, double zm, double zp, double Dz)
+{
+    if (ARITH == ARITH_STRICT) {
+        const double sz = __dadd_rn(__dsub_rn(zp, __dmul_rn(2.0, c)), zm);
+        return __dadd_rn(t, __dmul_rn(Dz, sz));
+    } else {
+        const double sz = __dadd_rn(__dsub_rn(zp, __dadd_rn(c, c)), zm);
+        return __fma_rn(sz, Dz, t);
+    }
+}
+
+// max over a warp of non-negative doubles, then one atomicMax on the bit pattern (order-preserving for >= 0).
+__device__ __forceinline__ void warp_residual_commit(double r, unsigned long long* slot)
+{
+    unsigned long long b = (unsigned long long)__double_as_longlong(r);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, b, o);
+        b = other > b ? other : b;
+    }
+    if ((threadIdx.x & 31) == 0 && b != 0ull) atomicMax(slot, b);
+}
+
+struct Geom {
+    int nx, ny;            // points per row / rows per plane
+    int pitch;             // doubles per row in memory
+    long long plane;       // doubles per plane in memory (pitch*ny)
+    int za, zb;            // local output plane range [za, zb); every plane in it is a global interior plane
+    double Dx, Dy, Dz;
+};
+
+// ------------------------------------------------------------------------------------------------------
+// IC + Dirichlet shell (reference heat3D.cu:409-453), written to both buffers, ghost planes included.
+// Order of the reference's writes: zero; y-top plane = 1.0; then x=0 / x=nx-1 / z=0 / z=nz-1 faces =
+// j*sp_y — so the four side faces win on the top edges.
+// ------------------------------------------------------------------------------------------------------
+__global__ void init_reference_field_kernel(double* __restrict__ a, double* __restrict__ b, int nx, int ny, int pitch,
+                                            int planes, long long zg0, int nz_global, double sp_y)
+{
+    const long long rows = (long long)ny * planes;
+    for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+        const int zl = (int)(row / ny), j = (int)(row % ny);
+        const long long zg = zg0 + zl;
+        const bool in_domain = zg >= 0 && zg < nz_global;
+        const bool zface = zg == 0 || zg == nz_global - 1;
+        double* ra = a + row * pitch;
+        double* rb = b + row * pitch;
+        for (int i = threadIdx.x; i < pitch; i += blockDim.x) {
+            double v = 0.0;
+            if (in_domain && i < nx) {
+                if (j == ny - 1) v = 1.0;
+                if (i == 0 || i == nx - 1 || zface) v = (double)j * sp_y;
+            }
+            ra[i] = v;
+            rb[i] = v;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Baseline stencil: thread per (x,y) column of a z-chunk, three z values in registers, xy neighbours
+// through L1.  First correct path; also the fallback for shapes the TMA kernel does not take.
+// ------------------------------------------------------------------------------------------------------
+template <int ARITH, bool RES>
+__global__ void __launch_bounds__(256) stencil_baseline_kernel(const double* __restrict__ src, double* __restrict__ dst,
+                                                               Geom g, int zchunk, unsigned long long* res_slot)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y * blockDim.y + threadIdx.y;
+    const int z0 = g.za + blockIdx.z * zchunk;
+    const int z1 = min(z0 + zchunk, g.zb);
+    const bool active = x >= 1 && x <= g.nx - 2 && y >= 1 && y <= g.ny - 2;
+    double rmax = 0.0;
+    if (active) {
+        const double* p = src + (long long)z0 * g.plane + (long long)y * g.pitch + x;
+        double* q = dst + (long long)z0 * g.plane + (long long)y * g.pitch + x;
+        double below = __ldg(p - g.plane), c = __ldg(p);
+        for (int z = z0; z < z1; ++z) {
+            const double above = __ldg(p + g.plane);
+            const double t = partial_xy<ARITH>(c, __ldg(p - 1), __ldg(p + 1), __ldg(p - g.pitch), __ldg(p + g.pitch), g.Dx, g.Dy);
+            const double r = finish_z<ARITH>(t, c, below, above, g.Dz);
+            *q = r;
+            if (RES) rmax = fmax(rmax, fabs(__dsub_rn(r, c)));
+            below = c;
+            c = above;
+            p += g.plane;
+            q += g.plane;
+        }
+    }
+    if (RES) warp_residual_commit(rmax, res_slot);
+}
+
+// ------------------------------------------------------------------------------------------------------
+// TMA-staged z-streaming stencil.
+//
+// Work = (xy tile, output plane) pairs, linearised tile-major / z-minor and cut into equal contiguous
+// runs, one per CTA (grid = SMs x CTAs/SM), so every CTA streams the same number of planes whatever the
+// grid shape.  A run is walked as segments (one tile, consecutive planes).  For a segment of n output
+// planes the producer warp TMA-loads n+2 input planes (box (TX+4) x (TY+2) x 1, i.e. the tile plus a
+// 2-column / 1-row halo; 2 columns keep every thread's pair of cells 16-byte aligned in shared memory)
+// into a STAGES-deep ring guarded by full/empty mbarriers.  Each consumer thread owns a 2(x) x RY(y)
+// patch of the tile for the whole segment: when plane p lands it reads its own cells and the four xy
+// neighbours from shared memory once, releases the stage, forms partial_xy(p), and finishes plane p-1
+// with finish_z using the centre values of planes p-2, p-1, p it keeps in registers; the finished pair
+// goes to HBM with one 128-bit store.  Dirichlet cells are never written (both buffers carry the shell).
+// ------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+            smem_u32(smem_dst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+
+template <int TX, int TY, int STAGES>
+struct TmaCfg {
+    static constexpr int ROW = TX + 4;                                // doubles per staged row
+    static constexpr int ROWS = TY + 2;                               // staged rows
+    static constexpr int STAGE_BYTES = ROW * ROWS * 8;                // bytes TMA delivers per plane
+    static constexpr int STAGE_STRIDE = (STAGE_BYTES + 127) / 128 * 128;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_STRIDE + 2 * STAGES * 8 + 128;  // +128: manual alignment slack
+};
+
+struct TmaWork {
+    int ntx, nty;          // tiles in x, y
+    long long total;       // ntx*nty*(zb-za) plane-tiles
+    long long per_cta;     // ceil(total / gridDim.x)
+};
+
+template <int TX, int TY, int RY, int STAGES, int ARITH, bool RES, int MINB>
+__global__ void __launch_bounds__((TX / 2) * (TY / RY) + 32, MINB)
+    stencil_tma_kernel(const __grid_constant__ CUtensorMap tmap, double* __restrict__ dst, Geom g, TmaWork w,
+                       unsigned long long* res_slot)
+{
+    using Cfg = TmaCfg<TX, TY, STAGES>;
+    constexpr int NCONS = (TX / 2) * (TY / RY);
+    constexpr int ROW = Cfg::ROW;
+    static_assert(TX % 64 == 0 && TY % RY == 0 && NCONS % 32 == 0, "tile shape");
+
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 127) & ~(uintptr_t)127);
+    uint64_t* full = (uint64_t*)(smem + STAGES * Cfg::STAGE_STRIDE);
+    uint64_t* empty = full + STAGES;
+
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], NCONS / 32);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    const int nzp = g.zb - g.za;
+    long long begin = (long long)blockIdx.x * w.per_cta;
+    const long long end = min(begin + w.per_cta, w.total);
+
+    if (tid >= NCONS) {
+        // ---------------- producer warp: one lane issues the TMA loads ----------------
+        if (tid == NCONS) {
+            uint32_t it = 0;
+            while (begin < end) {
+                const int tile = (int)(begin / nzp);
+                const int zoff = (int)(begin - (long long)tile * nzp);
+                const int cnt = (int)min((long long)(nzp - zoff), end - begin);
+                const int x0 = (tile % w.ntx) * TX - 2;
+                const int y0 = (tile / w.ntx) * TY - 1;
+                const int zs = g.za + zoff;
+                for (int p = zs - 1; p <= zs + cnt; ++p, ++it) {
+                    const uint32_t s = it % STAGES, ph = (it / STAGES) & 1u;
+                    mbar_wait(&empty[s], ph ^ 1u);
+                    mbar_arrive_expect_tx(&full[s], Cfg::STAGE_BYTES);
+                    tma_load_3d(smem + s * Cfg::STAGE_STRIDE, &tmap, &full[s], x0, y0, p);
+                }
+                begin += cnt;
+            }
+        }
+        return;
+    }
+
+    // ---------------- consumers ----------------
+    const int lx = tid % (TX / 2);
+    const int ry = tid / (TX / 2);
+    const int lane = tid & 31;
+    double rmax = 0.0;
+    uint32_t it = 0;
+
+    while (begin < end) {
+        const int tile = (int)(begin / nzp);
+        const int zoff = (int)(begin - (long long)tile * nzp);
+        const int cnt = (int)min((long long)(nzp - zoff), end - begin);
+        const int gx = (tile % w.ntx) * TX + 2 * lx;        // global x of this thread's first cell
+        const int gy = (tile / w.ntx) * TY + ry * RY;       // global y of this thread's first row
+        const int zs = g.za + zoff;
+        const bool vx0 = gx >= 1 && gx <= g.nx - 2;
+        const bool vx1 = gx + 1 <= g.nx - 2;                 // gx+1 >= 1 always
+        double* out = dst + (long long)(zs - 1) * g.plane + (long long)gy * g.pitch + gx;   // plane of "p-1" at q=1
+
+        double2 c1[RY], c2[RY], t1[RY];                      // centre at p-1, p-2; partial at p-1
+#pragma unroll
+        for (int r = 0; r < RY; ++r) c1[r] = c2[r] = t1[r] = make_double2(0.0, 0.0);
+
+        for (int q = 0; q <= cnt + 1; ++q, ++it) {
+            const uint32_t s = it % STAGES, ph = (it / STAGES) & 1u;
+            const double* S = (const double*)(smem + s * Cfg::STAGE_STRIDE) + (1 + ry * RY) * ROW + 2 + 2 * lx;
+            mbar_wait(&full[s], ph);
+            double2 cc[RY];
+            double xl[RY], xr[RY];
+            const double2 up = *(const double2*)(S - ROW);
+            const double2 dn = *(const double2*)(S + RY * ROW);
+#pragma unroll
+            for (int r = 0; r < RY; ++r) {
+                cc[r] = *(const double2*)(S + r * ROW);
+                xl[r] = S[r * ROW - 1];
+                xr[r] = S[r * ROW + 2];
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[s]);
+
+#pragma unroll
+            for (int r = 0; r < RY; ++r) {
+                const double2 ym = r == 0 ? up : cc[r - 1];
+                const double2 yp = r == RY - 1 ? dn : cc[r + 1];
+                double2 tn;
+                tn.x = partial_xy<ARITH>(cc[r].x, xl[r], cc[r].y, ym.x, yp.x, g.Dx, g.Dy);
+                tn.y = partial_xy<ARITH>(cc[r].y, cc[r].x, xr[r], ym.y, yp.y, g.Dx, g.Dy);
+                if (q >= 2) {
+                    double2 o;
+                    o.x = finish_z<ARITH>(t1[r].x, c1[r].x, c2[r].x, cc[r].x, g.Dz);
+                    o.y = finish_z<ARITH>(t1[r].y, c1[r].y, c2[r].y, cc[r].y, g.Dz);
+                    const int y = gy + r;
+                    if (y >= 1 && y <= g.ny - 2) {
+                        double* o_ptr = out + (long long)r * g.pitch;
+                        if (vx0 && vx1) {
+                            *(double2*)o_ptr = o;
+                            if (RES) rmax = fmax(rmax, fmax(fabs(__dsub_rn(o.x, c1[r].x)), fabs(__dsub_rn(o.y, c1[r].y))));
+                        } else if (vx0) {
+                            o_ptr[0] = o.x;
+                            if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o.x, c1[r].x)));
+                        } else if (vx1) {
+                            o_ptr[1] = o.y;
+                            if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o.y, c1[r].y)));
+                        }
+                    }
+                }
+                c2[r] = c1[r];
+                c1[r] = cc[r];
+                t1[r] = tn;
+            }
+            if (q >= 1) out += g.plane;
+        }
+        begin += cnt;
+    }
+    if (RES) warp_residual_commit(rmax, res_slot);
+}
+
+// ------------------------------------------------------------------------------------------------------
+// mean |T - j*sp_y| over interior cells (reference heat3D.cu:1096-1102): pass 1 writes one partial sum per
+// block into scratch (fixed block->cells mapping, fixed tree order => deterministic), pass 2 folds them.
+// ------------------------------------------------------------------------------------------------------
+template <int BLOCK>
+__device__ __forceinline__ double block_sum(double v)
+{
+    __shared__ double sh[BLOCK / 32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = 0.0;
+    if (threadIdx.x < 32) {
+        t = threadIdx.x < BLOCK / 32 ? sh[threadIdx.x] : 0.0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+    }
+    __syncthreads();
+    return t;   // valid in thread 0
+}
+
+// rows = (ny-2) * number of owned interior planes; row r -> plane za + r/(ny-2), y = 1 + r%(ny-2).
+__global__ void __launch_bounds__(256) abs_error_partial_kernel(const double* __restrict__ f, int nx, int ny, int pitch,
+                                                                long long plane, int za, int zb, double sp_y,
+                                                                double* __restrict__ partial)
+{
+    const long long rows = (long long)(ny - 2) * (zb - za);
+    double acc = 0.0;
+    for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
+        const int z = za + (int)(row / (ny - 2)), j = 1 + (int)(row % (ny - 2));
+        const double yj = (double)j * sp_y;
+        const double* p = f + (long long)z * plane + (long long)j * pitch;
+        for (int i = 1 + threadIdx.x; i <= nx - 2; i += 256) acc += fabs(__dsub_rn(p[i], yj));
+    }
+    const double s = block_sum<256>(acc);
+    if (threadIdx.x == 0) partial[blockIdx.x] = s;
+}
+
+__global__ void __launch_bounds__(256) sum_partials_kernel(const double* __restrict__ partial, int n, double* __restrict__ out)
+{
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n; i += 256) acc += partial[i];
+    const double s = block_sum<256>(acc);
+    if (threadIdx.x == 0) *out = s;
+}
+
+}  // namespace h3

@@ -133,7 +133,6 @@ const std::vector<TmaVariant>& variants()
     static const std::vector<TmaVariant> v = {
         make_variant<128, 32, 4, 4, 1>("tma_128x32_r4_s4_c1"),
         make_variant<128, 32, 4, 5, 1>("tma_128x32_r4_s5_c1"),
-        make_variant<128, 32, 2, 4, 1>("tma_128x32_r2_s4_c1"),
         make_variant<128, 16, 4, 4, 2>("tma_128x16_r4_s4_c2"),
         make_variant<128, 16, 2, 4, 2>("tma_128x16_r2_s4_c2"),
         make_variant<128, 16, 2, 5, 2>("tma_128x16_r2_s5_c2"),

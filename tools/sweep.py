@@ -16,7 +16,7 @@ try:
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
 except Exception:
     pass
-TUNES = [(128, 32, 4, 4, 1), (128, 32, 4, 5, 1), (128, 32, 2, 4, 1), (128, 16, 4, 4, 2), (128, 16, 2, 4, 2),
+TUNES = [(128, 32, 4, 4, 1), (128, 32, 4, 5, 1), (128, 16, 4, 4, 2), (128, 16, 2, 4, 2),
          (128, 16, 2, 5, 2), (128, 8, 2, 4, 4), (128, 8, 1, 6, 3), (64, 32, 4, 4, 2), (64, 16, 2, 4, 4), (64, 8, 2, 4, 4)]
 cells = (n - 2) ** 3
 rows = []

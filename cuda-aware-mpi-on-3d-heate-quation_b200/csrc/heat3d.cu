@@ -119,7 +119,7 @@ TmaVariant make_variant(const char* name)
     v.name = name;
     v.tx = TX; v.ty = TY; v.ry = RY; v.stages = ST; v.minb = MINB;
     v.smem = h3::TmaCfg<TX, TY, ST>::SMEM_BYTES;
-    v.threads = (TX / 2) * (TY / RY) + 32;
+    v.threads = (TX / 2) * (TY / RY);
     v.fn[0][0] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_STRICT, false, MINB>;
     v.fn[0][1] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_STRICT, true, MINB>;
     v.fn[1][0] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_FMA, false, MINB>;
@@ -131,16 +131,18 @@ TmaVariant make_variant(const char* name)
 const std::vector<TmaVariant>& variants()
 {
     static const std::vector<TmaVariant> v = {
-        make_variant<128, 32, 4, 4, 1>("tma_128x32_r4_s4_c1"),
-        make_variant<128, 32, 4, 5, 1>("tma_128x32_r4_s5_c1"),
-        make_variant<128, 16, 4, 4, 2>("tma_128x16_r4_s4_c2"),
+        make_variant<128, 8, 2, 4, 3>("tma_128x8_r2_s4_c3"),
+        make_variant<128, 8, 2, 3, 4>("tma_128x8_r2_s3_c4"),
+        make_variant<128, 8, 2, 5, 3>("tma_128x8_r2_s5_c3"),
+        make_variant<128, 8, 4, 4, 4>("tma_128x8_r4_s4_c4"),
+        make_variant<128, 8, 1, 4, 2>("tma_128x8_r1_s4_c2"),
         make_variant<128, 16, 2, 4, 2>("tma_128x16_r2_s4_c2"),
-        make_variant<128, 16, 2, 5, 2>("tma_128x16_r2_s5_c2"),
-        make_variant<128, 8, 2, 4, 4>("tma_128x8_r2_s4_c4"),
-        make_variant<128, 8, 1, 6, 3>("tma_128x8_r1_s6_c3"),
-        make_variant<64, 32, 4, 4, 2>("tma_64x32_r4_s4_c2"),
+        make_variant<128, 16, 4, 4, 2>("tma_128x16_r4_s4_c2"),
+        make_variant<128, 16, 4, 3, 3>("tma_128x16_r4_s3_c3"),
+        make_variant<128, 32, 4, 4, 1>("tma_128x32_r4_s4_c1"),
+        make_variant<128, 32, 2, 4, 1>("tma_128x32_r2_s4_c1"),
         make_variant<64, 16, 2, 4, 4>("tma_64x16_r2_s4_c4"),
-        make_variant<64, 8, 2, 4, 4>("tma_64x8_r2_s4_c4"),
+        make_variant<64, 8, 2, 4, 6>("tma_64x8_r2_s4_c6"),
     };
     return v;
 }
@@ -206,9 +208,12 @@ int make_tmap(Slab& s, int which, const heat3d_ctx* c)
     cuuint64_t strides[2] = {(cuuint64_t)s.pitch * 8, (cuuint64_t)s.plane * 8};
     cuuint32_t box[3] = {(cuuint32_t)(v.tx + 4), (cuuint32_t)(v.ty + 2), 1};
     cuuint32_t estr[3] = {1, 1, 1};
+    // L2 promotion widens every L2 miss to 128/256 B; the staged rows start 16 B before a 128-B boundary, so
+    // promotion would drag in whole extra lines per row.  Default: none.  (HEAT3D_TMA_L2PROMO=0..3 for experiments.)
+    CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_NONE;
+    if (const char* e = getenv("HEAT3D_TMA_L2PROMO")) promo = (CUtensorMapL2promotion)atoi(e);
     CUresult r = g_encode(&s.tmap[which], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, s.buf[which], dims, strides, box, estr,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
     return HEAT3D_OK;
 }
@@ -227,11 +232,18 @@ int launch_stencil(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res)
         h3::TmaWork w;
         w.ntx = ((int)c->p.nx + v.tx - 1) / v.tx;
         w.nty = ((int)c->p.ny + v.ty - 1) / v.ty;
-        w.total = (long long)w.ntx * w.nty * (zb - za);
-        long long grid = (long long)s.num_sms * v.minb;
-        if (grid > w.total) grid = w.total;
-        w.per_cta = (w.total + grid - 1) / grid;
-        grid = (w.total + w.per_cta - 1) / w.per_cta;
+        const int nzp = zb - za;
+        const long long ntiles = (long long)w.ntx * w.nty, slots = (long long)s.num_sms * v.minb;
+        // z-chunks: short chunks (default 16 output planes, tune[5] overrides) make the grid sweep the domain
+        // z-major, wave after wave, so the planes a wave touches - and the halos its tiles share - stay in L2;
+        // but never fewer chunks than it takes to fill every resident CTA slot once.
+        int clen = c->p.tune[5] > 0 ? c->p.tune[5] : 16;
+        long long nch = (nzp + clen - 1) / clen;
+        if (nch * ntiles < slots) nch = (slots + ntiles - 1) / ntiles;
+        if (nch > nzp) nch = nzp;
+        w.chunk_len = (int)((nzp + nch - 1) / nch);
+        w.nchunks = (nzp + w.chunk_len - 1) / w.chunk_len;
+        const long long grid = ntiles * w.nchunks;
         void* args[] = {(void*)&s.tmap[src], (void*)&dst, (void*)&g, (void*)&w, (void*)&s.d_res};
         CU_TRY(cudaLaunchKernel(v.fn[ar][res ? 1 : 0], dim3((unsigned)grid), dim3(v.threads), args, v.smem, s.compute));
     } else {
@@ -777,8 +789,10 @@ int heat3d_upload_planes(heat3d_ctx* c, const double* host, uint32_t z0, uint32_
         if (b <= a) continue;
         if ((rc = set_dev(s))) return rc;
         const uint32_t zl = a - s.z0 + s.G;
-        for (int w = 0; w < 2; ++w)   // both buffers carry the Dirichlet shell
-            if ((rc = copy_planes(s, w, c->p.nx, c->p.ny, zl, b - a, const_cast<double*>(host) + (size_t)(a - z0) * plane_host, true, s.compute))) return rc;
+        // one trip over PCIe into the current buffer, then an on-device copy: both buffers carry the Dirichlet shell
+        if ((rc = copy_planes(s, c->cur, c->p.nx, c->p.ny, zl, b - a, const_cast<double*>(host) + (size_t)(a - z0) * plane_host, true, s.compute))) return rc;
+        CU_TRY(cudaMemcpyAsync(s.buf[c->cur ^ 1] + (long long)zl * s.plane, s.buf[c->cur] + (long long)zl * s.plane,
+                               (size_t)(b - a) * s.plane * sizeof(double), cudaMemcpyDeviceToDevice, s.compute));
     }
     // refresh ghost planes of both buffers from the neighbours
     for (Slab& s : c->slabs) {

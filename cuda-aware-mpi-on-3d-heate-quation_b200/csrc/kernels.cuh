@@ -133,26 +133,24 @@ __global__ void __launch_bounds__(256) stencil_baseline_kernel(const double* __r
 // ------------------------------------------------------------------------------------------------------
 // TMA-staged z-streaming stencil.
 //
-// Work = (xy tile, output plane) pairs, linearised tile-major / z-minor and cut into equal contiguous
-// runs, one per CTA (grid = SMs x CTAs/SM), so every CTA streams the same number of planes whatever the
-// grid shape.  A run is walked as segments (one tile, consecutive planes).  For a segment of n output
-// planes the producer warp TMA-loads n+2 input planes (box (TX+4) x (TY+2) x 1, i.e. the tile plus a
-// 2-column / 1-row halo; 2 columns keep every thread's pair of cells 16-byte aligned in shared memory)
-// into a STAGES-deep ring guarded by full/empty mbarriers.  Each consumer thread owns a 2(x) x RY(y)
-// patch of the tile for the whole segment: when plane p lands it reads its own cells and the four xy
-// neighbours from shared memory once, releases the stage, forms partial_xy(p), and finishes plane p-1
-// with finish_z using the centre values of planes p-2, p-1, p it keeps in registers; the finished pair
-// goes to HBM with one 128-bit store.  Dirichlet cells are never written (both buffers carry the shell).
+// Work = xy tiles x z-chunks; CTA b takes tile b % ntiles of chunk b / ntiles, so CTAs that are resident
+// together sweep neighbouring tiles through the same planes at the same time and each other's halo
+// columns/rows are L2 hits rather than second trips to HBM.  For a chunk of n output planes the CTA
+// TMA-loads n+2 input planes (box (TX+4) x (TY+2) x 1: the tile plus a 2-column / 1-row halo; 2 columns
+// keep every thread's pair of cells 16-byte aligned in shared memory) through a STAGES-deep ring.  There
+// is no producer warp: the warp that is LAST to finish reading a stage (an acq_rel shared-memory counter
+// tells it so) re-arms that stage's mbarrier and issues the TMA load that will next land in it, so no
+// thread ever waits for a stage to drain.  Each thread owns a 2(x) x RY(y) patch of the tile for the
+// whole chunk: when plane p lands it reads its own cells and the four xy neighbours from shared memory
+// once, releases the stage, forms partial_xy(p), and finishes plane p-1 with finish_z from the centre
+// values of planes p-2, p-1, p it keeps in registers; the finished pair goes to HBM as one 128-bit store.
+// Dirichlet cells are never written (both buffers carry the shell).
 // ------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
 {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
-{
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
 {
@@ -180,6 +178,13 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m
         "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
+// arrival counter with release (my reads are done) / acquire (I see everyone else's) semantics
+__device__ __forceinline__ uint32_t smem_arrive_count(uint32_t* ctr)
+{
+    uint32_t old;
+    asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(smem_u32(ctr)) : "memory");
+    return old;
+}
 
 template <int TX, int TY, int STAGES>
 struct TmaCfg {
@@ -187,141 +192,130 @@ struct TmaCfg {
     static constexpr int ROWS = TY + 2;                               // staged rows
     static constexpr int STAGE_BYTES = ROW * ROWS * 8;                // bytes TMA delivers per plane
     static constexpr int STAGE_STRIDE = (STAGE_BYTES + 127) / 128 * 128;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_STRIDE + 2 * STAGES * 8 + 128;  // +128: manual alignment slack
+    static constexpr int SMEM_BYTES = STAGES * STAGE_STRIDE + STAGES * 8 + STAGES * 4 + 128;  // +128: alignment slack
 };
 
 struct TmaWork {
     int ntx, nty;          // tiles in x, y
-    long long total;       // ntx*nty*(zb-za) plane-tiles
-    long long per_cta;     // ceil(total / gridDim.x)
+    int nchunks;           // z-chunks
+    int chunk_len;         // output planes per chunk (last one may be shorter)
 };
 
 template <int TX, int TY, int RY, int STAGES, int ARITH, bool RES, int MINB>
-__global__ void __launch_bounds__((TX / 2) * (TY / RY) + 32, MINB)
+__global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
     stencil_tma_kernel(const __grid_constant__ CUtensorMap tmap, double* __restrict__ dst, Geom g, TmaWork w,
                        unsigned long long* res_slot)
 {
     using Cfg = TmaCfg<TX, TY, STAGES>;
-    constexpr int NCONS = (TX / 2) * (TY / RY);
+    constexpr int NTHR = (TX / 2) * (TY / RY);
+    constexpr int NWARP = NTHR / 32;
     constexpr int ROW = Cfg::ROW;
-    static_assert(TX % 64 == 0 && TY % RY == 0 && NCONS % 32 == 0, "tile shape");
+    static_assert(TX % 64 == 0 && TY % RY == 0 && NTHR % 32 == 0 && NTHR <= 1024, "tile shape");
 
     extern __shared__ unsigned char smem_raw[];
     unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 127) & ~(uintptr_t)127);
     uint64_t* full = (uint64_t*)(smem + STAGES * Cfg::STAGE_STRIDE);
-    uint64_t* empty = full + STAGES;
+    uint32_t* drained = (uint32_t*)(full + STAGES);
 
     const int tid = threadIdx.x;
+    const int ntiles = w.ntx * w.nty;
+    const int tile = blockIdx.x % ntiles;
+    const int chunk = blockIdx.x / ntiles;
+    const int zs = g.za + chunk * w.chunk_len;                  // first output plane of this CTA
+    const int cnt = min(w.chunk_len, g.zb - zs);                // output planes of this CTA
+    if (cnt <= 0) return;
+    const int niter = cnt + 2;                                  // input planes zs-1 .. zs+cnt
+    const int bx = (tile % w.ntx) * TX - 2;                     // TMA box origin
+    const int by = (tile / w.ntx) * TY - 1;
+
     if (tid == 0) {
 #pragma unroll
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full[s], 1);
-            mbar_init(&empty[s], NCONS / 32);
+            drained[s] = 0;
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s)
+            if (s < niter) {
+                mbar_arrive_expect_tx(&full[s], Cfg::STAGE_BYTES);
+                tma_load_3d(smem + s * Cfg::STAGE_STRIDE, &tmap, &full[s], bx, by, zs - 1 + s);
+            }
     }
     __syncthreads();
 
-    const int nzp = g.zb - g.za;
-    long long begin = (long long)blockIdx.x * w.per_cta;
-    const long long end = min(begin + w.per_cta, w.total);
-
-    if (tid >= NCONS) {
-        // ---------------- producer warp: one lane issues the TMA loads ----------------
-        if (tid == NCONS) {
-            uint32_t it = 0;
-            while (begin < end) {
-                const int tile = (int)(begin / nzp);
-                const int zoff = (int)(begin - (long long)tile * nzp);
-                const int cnt = (int)min((long long)(nzp - zoff), end - begin);
-                const int x0 = (tile % w.ntx) * TX - 2;
-                const int y0 = (tile / w.ntx) * TY - 1;
-                const int zs = g.za + zoff;
-                for (int p = zs - 1; p <= zs + cnt; ++p, ++it) {
-                    const uint32_t s = it % STAGES, ph = (it / STAGES) & 1u;
-                    mbar_wait(&empty[s], ph ^ 1u);
-                    mbar_arrive_expect_tx(&full[s], Cfg::STAGE_BYTES);
-                    tma_load_3d(smem + s * Cfg::STAGE_STRIDE, &tmap, &full[s], x0, y0, p);
-                }
-                begin += cnt;
-            }
-        }
-        return;
-    }
-
-    // ---------------- consumers ----------------
     const int lx = tid % (TX / 2);
     const int ry = tid / (TX / 2);
     const int lane = tid & 31;
+    const int gx = bx + 2 + 2 * lx;                             // global x of this thread's first cell
+    const int gy = by + 1 + ry * RY;                            // global y of this thread's first row
+    const bool vx0 = gx >= 1 && gx <= g.nx - 2;
+    const bool vx1 = gx + 1 <= g.nx - 2;                        // gx+1 >= 1 always
+    double* out = dst + (long long)(zs - 1) * g.plane + (long long)gy * g.pitch + gx;   // plane "p-1" at q = 1
+    const int soff = (1 + ry * RY) * ROW + 2 + 2 * lx;          // own first cell inside a stage
     double rmax = 0.0;
-    uint32_t it = 0;
 
-    while (begin < end) {
-        const int tile = (int)(begin / nzp);
-        const int zoff = (int)(begin - (long long)tile * nzp);
-        const int cnt = (int)min((long long)(nzp - zoff), end - begin);
-        const int gx = (tile % w.ntx) * TX + 2 * lx;        // global x of this thread's first cell
-        const int gy = (tile / w.ntx) * TY + ry * RY;       // global y of this thread's first row
-        const int zs = g.za + zoff;
-        const bool vx0 = gx >= 1 && gx <= g.nx - 2;
-        const bool vx1 = gx + 1 <= g.nx - 2;                 // gx+1 >= 1 always
-        double* out = dst + (long long)(zs - 1) * g.plane + (long long)gy * g.pitch + gx;   // plane of "p-1" at q=1
-
-        double2 c1[RY], c2[RY], t1[RY];                      // centre at p-1, p-2; partial at p-1
+    double2 c1[RY], c2[RY], t1[RY];                             // centre at p-1, p-2; partial at p-1
 #pragma unroll
-        for (int r = 0; r < RY; ++r) c1[r] = c2[r] = t1[r] = make_double2(0.0, 0.0);
+    for (int r = 0; r < RY; ++r) c1[r] = c2[r] = t1[r] = make_double2(0.0, 0.0);
 
-        for (int q = 0; q <= cnt + 1; ++q, ++it) {
-            const uint32_t s = it % STAGES, ph = (it / STAGES) & 1u;
-            const double* S = (const double*)(smem + s * Cfg::STAGE_STRIDE) + (1 + ry * RY) * ROW + 2 + 2 * lx;
-            mbar_wait(&full[s], ph);
-            double2 cc[RY];
-            double xl[RY], xr[RY];
-            const double2 up = *(const double2*)(S - ROW);
-            const double2 dn = *(const double2*)(S + RY * ROW);
+    uint32_t s = 0, ph = 0;
+    for (int q = 0; q < niter; ++q) {
+        const double* S = (const double*)(smem + s * Cfg::STAGE_STRIDE) + soff;
+        mbar_wait(&full[s], ph);
+        double2 cc[RY];
+        double xl[RY], xr[RY];
+        const double2 up = *(const double2*)(S - ROW);
+        const double2 dn = *(const double2*)(S + RY * ROW);
 #pragma unroll
-            for (int r = 0; r < RY; ++r) {
-                cc[r] = *(const double2*)(S + r * ROW);
-                xl[r] = S[r * ROW - 1];
-                xr[r] = S[r * ROW + 2];
+        for (int r = 0; r < RY; ++r) {
+            cc[r] = *(const double2*)(S + r * ROW);
+            xl[r] = S[r * ROW - 1];
+            xr[r] = S[r * ROW + 2];
+        }
+        __syncwarp();
+        if (lane == 0) {
+            const uint32_t old = smem_arrive_count(&drained[s]);
+            if (old % NWARP == NWARP - 1 && q + STAGES < niter) {      // last reader refills the stage
+                mbar_arrive_expect_tx(&full[s], Cfg::STAGE_BYTES);
+                tma_load_3d(smem + s * Cfg::STAGE_STRIDE, &tmap, &full[s], bx, by, zs - 1 + q + STAGES);
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[s]);
+        }
+        __syncwarp();
 
 #pragma unroll
-            for (int r = 0; r < RY; ++r) {
-                const double2 ym = r == 0 ? up : cc[r - 1];
-                const double2 yp = r == RY - 1 ? dn : cc[r + 1];
-                double2 tn;
-                tn.x = partial_xy<ARITH>(cc[r].x, xl[r], cc[r].y, ym.x, yp.x, g.Dx, g.Dy);
-                tn.y = partial_xy<ARITH>(cc[r].y, cc[r].x, xr[r], ym.y, yp.y, g.Dx, g.Dy);
-                if (q >= 2) {
-                    double2 o;
-                    o.x = finish_z<ARITH>(t1[r].x, c1[r].x, c2[r].x, cc[r].x, g.Dz);
-                    o.y = finish_z<ARITH>(t1[r].y, c1[r].y, c2[r].y, cc[r].y, g.Dz);
-                    const int y = gy + r;
-                    if (y >= 1 && y <= g.ny - 2) {
-                        double* o_ptr = out + (long long)r * g.pitch;
-                        if (vx0 && vx1) {
-                            *(double2*)o_ptr = o;
-                            if (RES) rmax = fmax(rmax, fmax(fabs(__dsub_rn(o.x, c1[r].x)), fabs(__dsub_rn(o.y, c1[r].y))));
-                        } else if (vx0) {
-                            o_ptr[0] = o.x;
-                            if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o.x, c1[r].x)));
-                        } else if (vx1) {
-                            o_ptr[1] = o.y;
-                            if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o.y, c1[r].y)));
-                        }
+        for (int r = 0; r < RY; ++r) {
+            const double2 ym = r == 0 ? up : cc[r - 1];
+            const double2 yp = r == RY - 1 ? dn : cc[r + 1];
+            double2 tn;
+            tn.x = partial_xy<ARITH>(cc[r].x, xl[r], cc[r].y, ym.x, yp.x, g.Dx, g.Dy);
+            tn.y = partial_xy<ARITH>(cc[r].y, cc[r].x, xr[r], ym.y, yp.y, g.Dx, g.Dy);
+            if (q >= 2) {
+                double2 o;
+                o.x = finish_z<ARITH>(t1[r].x, c1[r].x, c2[r].x, cc[r].x, g.Dz);
+                o.y = finish_z<ARITH>(t1[r].y, c1[r].y, c2[r].y, cc[r].y, g.Dz);
+                const int y = gy + r;
+                if (y >= 1 && y <= g.ny - 2) {
+                    double* o_ptr = out + (long long)r * g.pitch;
+                    if (vx0 && vx1) {
+                        *(double2*)o_ptr = o;
+                        if (RES) rmax = fmax(rmax, fmax(fabs(__dsub_rn(o.x, c1[r].x)), fabs(__dsub_rn(o.y, c1[r].y))));
+                    } else if (vx0) {
+                        o_ptr[0] = o.x;
+                        if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o.x, c1[r].x)));
+                    } else if (vx1) {
+                        o_ptr[1] = o.y;
+                        if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o.y, c1[r].y)));
                     }
                 }
-                c2[r] = c1[r];
-                c1[r] = cc[r];
-                t1[r] = tn;
             }
-            if (q >= 1) out += g.plane;
+            c2[r] = c1[r];
+            c1[r] = cc[r];
+            t1[r] = tn;
         }
-        begin += cnt;
+        if (q >= 1) out += g.plane;
+        if (++s == STAGES) { s = 0; ph ^= 1u; }
     }
     if (RES) warp_residual_commit(rmax, res_slot);
 }

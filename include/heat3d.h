@@ -75,7 +75,7 @@ typedef struct heat3d_params {
     void* stream;               /* optional cudaStream_t to use as compute stream (nlocal == 1 only)       */
     uint32_t flags;             /* HEAT3D_FLAG_*                                                           */
     int32_t tune[6];            /* kernel tuning overrides (0 = default): tile_x, tile_y, rows_per_thread,
-                                   stages, ctas_per_sm, reserved                                           */
+                                   stages, ctas_per_sm, chunk_len                                         */
 } heat3d_params;
 
 #define HEAT3D_FLAG_NO_OVERLAP 0x1u /* serialise halo exchange after compute (for exposed-halo measurement) */

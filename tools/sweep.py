@@ -16,12 +16,15 @@ try:
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
 except Exception:
     pass
-TUNES = [(128, 32, 4, 4, 1), (128, 32, 4, 5, 1), (128, 16, 4, 4, 2), (128, 16, 2, 4, 2),
-         (128, 16, 2, 5, 2), (128, 8, 2, 4, 4), (128, 8, 1, 6, 3), (64, 32, 4, 4, 2), (64, 16, 2, 4, 4), (64, 8, 2, 4, 4)]
+TUNES = [(128, 8, 2, 4, 3), (128, 8, 2, 3, 4), (128, 8, 2, 5, 3), (128, 8, 4, 4, 4), (128, 8, 1, 4, 2), (128, 16, 2, 4, 2),
+         (128, 16, 4, 4, 2), (128, 16, 4, 3, 3), (128, 32, 4, 4, 1), (128, 32, 2, 4, 1), (64, 16, 2, 4, 4), (64, 8, 2, 4, 6)]
 cells = (n - 2) ** 3
 rows = []
+extra = [dict(kernel=2, tune=t + (c,)) for t in [(128, 8, 2, 4, 3), (128, 16, 2, 4, 2), (128, 8, 4, 4, 4)] for c in (8, 12, 24, 32)]
+if os.environ.get("SWEEP_ONLY_EXTRA"):
+    TUNES = []
 for arith in (0, 1):
-    for kw in [dict(kernel=1)] + [dict(kernel=2, tune=t) for t in TUNES]:
+    for kw in ([dict(kernel=1)] if TUNES else []) + [dict(kernel=2, tune=t) for t in TUNES] + (extra if arith == 0 else []):
         try:
             with h3.Heat3D(n, n, n, arith=arith, **kw) as sim:
                 sim.init_reference_field()
@@ -33,7 +36,7 @@ for arith in (0, 1):
                     best = min(best, sim.timing()["last_call_ms"])
                 name = sim.kernel_name()
             glups = cells * steps / (best * 1e-3) / 1e9
-            rows.append((name, arith, best / steps, glups, glups * 16, glups * 16 / peak))
-            print("%-24s arith=%d  %.4f ms/step  %7.1f GLUPS  %7.1f GB/s  %.3f of measured HBM peak" % rows[-1], flush=True)
+            rows.append((name, str(kw.get("tune", ""))[-5:], arith, best / steps, glups, glups * 16, glups * 16 / peak))
+            print("%-24s %-5s arith=%d  %.4f ms/step  %7.1f GLUPS  %7.1f GB/s  %.3f of measured HBM peak" % rows[-1], flush=True)
         except Exception as e:  # keep sweeping
             print("FAILED", kw, e, flush=True)

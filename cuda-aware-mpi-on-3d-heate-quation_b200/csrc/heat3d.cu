@@ -132,17 +132,17 @@ const std::vector<TmaVariant>& variants()
 {
     static const std::vector<TmaVariant> v = {
         make_variant<128, 8, 2, 4, 3>("tma_128x8_r2_s4_c3"),
-        make_variant<128, 8, 2, 3, 4>("tma_128x8_r2_s3_c4"),
         make_variant<128, 8, 2, 5, 3>("tma_128x8_r2_s5_c3"),
         make_variant<128, 8, 4, 4, 4>("tma_128x8_r4_s4_c4"),
-        make_variant<128, 8, 1, 4, 2>("tma_128x8_r1_s4_c2"),
-        make_variant<128, 16, 2, 4, 2>("tma_128x16_r2_s4_c2"),
+        make_variant<128, 8, 4, 5, 4>("tma_128x8_r4_s5_c4"),
+        make_variant<128, 16, 2, 4, 1>("tma_128x16_r2_s4_c1"),
         make_variant<128, 16, 4, 4, 2>("tma_128x16_r4_s4_c2"),
-        make_variant<128, 16, 4, 3, 3>("tma_128x16_r4_s3_c3"),
+        make_variant<128, 16, 4, 5, 2>("tma_128x16_r4_s5_c2"),
+        make_variant<128, 16, 8, 4, 2>("tma_128x16_r8_s4_c2"),
         make_variant<128, 32, 4, 4, 1>("tma_128x32_r4_s4_c1"),
-        make_variant<128, 32, 2, 4, 1>("tma_128x32_r2_s4_c1"),
-        make_variant<64, 16, 2, 4, 4>("tma_64x16_r2_s4_c4"),
-        make_variant<64, 8, 2, 4, 6>("tma_64x8_r2_s4_c6"),
+        make_variant<128, 32, 4, 5, 1>("tma_128x32_r4_s5_c1"),
+        make_variant<128, 32, 8, 5, 1>("tma_128x32_r8_s5_c1"),
+        make_variant<64, 16, 4, 4, 4>("tma_64x16_r4_s4_c4"),
     };
     return v;
 }

@@ -21,6 +21,26 @@ namespace h3 {
 
 enum { ARITH_STRICT = 0, ARITH_FMA = 1 };
 
+// twice(c) is exact in both modes (2.0*c == c+c), so one value serves partial_xy and finish_z.
+__device__ __forceinline__ double twice(double c) { return __dadd_rn(c, c); }
+
+template <int ARITH>
+__device__ __forceinline__ double partial_xy2(double c, double c2, double xm, double xp, double ym, double yp, double Dx, double Dy)
+{
+    const double sx = __dadd_rn(__dsub_rn(xp, c2), xm);
+    const double sy = __dadd_rn(__dsub_rn(yp, c2), ym);
+    if (ARITH == ARITH_STRICT) return __dadd_rn(__dadd_rn(c, __dmul_rn(Dx, sx)), __dmul_rn(Dy, sy));
+    return __fma_rn(sy, Dy, __fma_rn(sx, Dx, c));
+}
+
+template <int ARITH>
+__device__ __forceinline__ double finish_z2(double t, double c2, double zm, double zp, double Dz)
+{
+    const double sz = __dadd_rn(__dsub_rn(zp, c2), zm);
+    if (ARITH == ARITH_STRICT) return __dadd_rn(t, __dmul_rn(Dz, sz));
+    return __fma_rn(sz, Dz, t);
+}
+
 template <int ARITH>
 __device__ __forceinline__ double partial_xy(double c, double xm, double xp, double ym, double yp, double Dx, double Dy)
 {
@@ -137,10 +157,10 @@ __global__ void __launch_bounds__(256) stencil_baseline_kernel(const double* __r
 // together sweep neighbouring tiles through the same planes at the same time and each other's halo
 // columns/rows are L2 hits rather than second trips to HBM.  For a chunk of n output planes the CTA
 // TMA-loads n+2 input planes (box (TX+4) x (TY+2) x 1: the tile plus a 2-column / 1-row halo; 2 columns
-// keep every thread's pair of cells 16-byte aligned in shared memory) through a STAGES-deep ring.  There
-// is no producer warp: the warp that is LAST to finish reading a stage (an acq_rel shared-memory counter
-// tells it so) re-arms that stage's mbarrier and issues the TMA load that will next land in it, so no
-// thread ever waits for a stage to drain.  Each thread owns a 2(x) x RY(y) patch of the tile for the
+// keep every thread's pair of cells 16-byte aligned in shared memory) through a STAGES-deep ring guarded by
+// full/empty mbarriers.  There is no producer warp (a 17th warp would cost every warp registers): the
+// refill duty rotates over the compute warps and runs one plane behind the readers, so it never spins on
+// a stage that is still being read.  Each thread owns a 2(x) x RY(y) patch of the tile for the
 // whole chunk: when plane p lands it reads its own cells and the four xy neighbours from shared memory
 // once, releases the stage, forms partial_xy(p), and finishes plane p-1 with finish_z from the centre
 // values of planes p-2, p-1, p it keeps in registers; the finished pair goes to HBM as one 128-bit store.
@@ -151,6 +171,10 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
 {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
 {
@@ -178,21 +202,13 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m
         "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
-// arrival counter with release (my reads are done) / acquire (I see everyone else's) semantics
-__device__ __forceinline__ uint32_t smem_arrive_count(uint32_t* ctr)
-{
-    uint32_t old;
-    asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(smem_u32(ctr)) : "memory");
-    return old;
-}
-
 template <int TX, int TY, int STAGES>
 struct TmaCfg {
     static constexpr int ROW = TX + 4;                                // doubles per staged row
     static constexpr int ROWS = TY + 2;                               // staged rows
     static constexpr int STAGE_BYTES = ROW * ROWS * 8;                // bytes TMA delivers per plane
     static constexpr int STAGE_STRIDE = (STAGE_BYTES + 127) / 128 * 128;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_STRIDE + STAGES * 8 + STAGES * 4 + 128;  // +128: alignment slack
+    static constexpr int SMEM_BYTES = STAGES * STAGE_STRIDE + 2 * STAGES * 8;
 };
 
 struct TmaWork {
@@ -200,6 +216,59 @@ struct TmaWork {
     int nchunks;           // z-chunks
     int chunk_len;         // output planes per chunk (last one may be shorter)
 };
+
+// Per-thread store plan, fixed for the whole chunk: which of the thread's cells exist and are interior.
+struct StorePlan {
+    bool all;          // every cell of the 2 x RY patch is an interior cell: plain 128-bit stores
+    bool x0, x1;       // first / second column is interior
+    uint32_t rows;     // bit r: row r is interior
+};
+
+template <int RY, int ARITH, bool RES, bool FINISH>
+__device__ __forceinline__ void plane_update(const double* __restrict__ S, int row_pitch, double2 (&cn)[RY], const double2 (&cp1)[RY],
+                                             const double2 (&cp2)[RY], double2 (&t)[RY], double2 (&tw)[RY],
+                                             double* __restrict__ out, int pitch, const StorePlan& sp, double Dx, double Dy,
+                                             double Dz, double& rmax)
+{
+    // one visit to the staged plane: own cells, x neighbours (left of .x, right of .y), y neighbours above/below the patch
+    double xl[RY], xr[RY];
+    const double2 up = *(const double2*)(S - row_pitch);
+    const double2 dn = *(const double2*)(S + RY * row_pitch);
+#pragma unroll
+    for (int r = 0; r < RY; ++r) {
+        cn[r] = *(const double2*)(S + r * row_pitch);
+        xl[r] = S[r * row_pitch - 1];
+        xr[r] = S[r * row_pitch + 2];
+    }
+#pragma unroll
+    for (int r = 0; r < RY; ++r) {
+        if (FINISH) {      // plane p-1: t and tw (= 2 * centre) were formed when it was staged
+            double2 o;
+            o.x = finish_z2<ARITH>(t[r].x, tw[r].x, cp2[r].x, cn[r].x, Dz);
+            o.y = finish_z2<ARITH>(t[r].y, tw[r].y, cp2[r].y, cn[r].y, Dz);
+            double* o_ptr = out + (long long)r * pitch;
+            if (sp.all) {
+                *(double2*)o_ptr = o;
+                if (RES) rmax = fmax(rmax, fmax(fabs(__dsub_rn(o.x, cp1[r].x)), fabs(__dsub_rn(o.y, cp1[r].y))));
+            } else if ((sp.rows >> r) & 1u) {
+                if (sp.x0) {
+                    o_ptr[0] = o.x;
+                    if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o.x, cp1[r].x)));
+                }
+                if (sp.x1) {
+                    o_ptr[1] = o.y;
+                    if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o.y, cp1[r].y)));
+                }
+            }
+        }
+        const double2 ym = r == 0 ? up : cn[r - 1];
+        const double2 yp = r == RY - 1 ? dn : cn[r + 1];
+        tw[r].x = twice(cn[r].x);
+        tw[r].y = twice(cn[r].y);
+        t[r].x = partial_xy2<ARITH>(cn[r].x, tw[r].x, xl[r], cn[r].y, ym.x, yp.x, Dx, Dy);
+        t[r].y = partial_xy2<ARITH>(cn[r].y, tw[r].y, cn[r].x, xr[r], ym.y, yp.y, Dx, Dy);
+    }
+}
 
 template <int TX, int TY, int RY, int STAGES, int ARITH, bool RES, int MINB>
 __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
@@ -211,11 +280,11 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
     constexpr int NWARP = NTHR / 32;
     constexpr int ROW = Cfg::ROW;
     static_assert(TX % 64 == 0 && TY % RY == 0 && NTHR % 32 == 0 && NTHR <= 1024, "tile shape");
+    static_assert(STAGES >= 3, "the refill runs one plane behind the readers");
 
-    extern __shared__ unsigned char smem_raw[];
-    unsigned char* smem = (unsigned char*)(((uintptr_t)smem_raw + 127) & ~(uintptr_t)127);
+    extern __shared__ __align__(128) unsigned char smem[];      // stages | full barriers | empty barriers
     uint64_t* full = (uint64_t*)(smem + STAGES * Cfg::STAGE_STRIDE);
-    uint32_t* drained = (uint32_t*)(full + STAGES);
+    uint64_t* empty = full + STAGES;
 
     const int tid = threadIdx.x;
     const int ntiles = w.ntx * w.nty;
@@ -232,7 +301,7 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
 #pragma unroll
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full[s], 1);
-            drained[s] = 0;
+            mbar_init(&empty[s], NWARP);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -248,74 +317,103 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
     const int lx = tid % (TX / 2);
     const int ry = tid / (TX / 2);
     const int lane = tid & 31;
+    const int warp = tid >> 5;
     const int gx = bx + 2 + 2 * lx;                             // global x of this thread's first cell
     const int gy = by + 1 + ry * RY;                            // global y of this thread's first row
-    const bool vx0 = gx >= 1 && gx <= g.nx - 2;
-    const bool vx1 = gx + 1 <= g.nx - 2;                        // gx+1 >= 1 always
-    double* out = dst + (long long)(zs - 1) * g.plane + (long long)gy * g.pitch + gx;   // plane "p-1" at q = 1
+    StorePlan sp;
+    sp.x0 = gx >= 1 && gx <= g.nx - 2;
+    sp.x1 = gx + 1 <= g.nx - 2;                                 // gx+1 >= 1 always
+    sp.rows = 0;
+#pragma unroll
+    for (int r = 0; r < RY; ++r)
+        if (gy + r >= 1 && gy + r <= g.ny - 2) sp.rows |= 1u << r;
+    sp.all = sp.x0 && sp.x1 && sp.rows == (1u << RY) - 1u;
+    double* out = dst + (long long)zs * g.plane + (long long)gy * g.pitch + gx;
     const int soff = (1 + ry * RY) * ROW + 2 + 2 * lx;          // own first cell inside a stage
     double rmax = 0.0;
 
-    double2 c1[RY], c2[RY], t1[RY];                             // centre at p-1, p-2; partial at p-1
+    // centre values of the three most recent planes rotate through C[0..2] (the plane loop is unrolled by 3
+    // so the rotation costs no register moves); t / tw hold partial_xy and 2*centre of the newest complete plane.
+    double2 C[3][RY], t[RY], tw[RY];
 #pragma unroll
-    for (int r = 0; r < RY; ++r) c1[r] = c2[r] = t1[r] = make_double2(0.0, 0.0);
+    for (int r = 0; r < RY; ++r) t[r] = tw[r] = make_double2(0.0, 0.0);
 
-    uint32_t s = 0, ph = 0;
-    for (int q = 0; q < niter; ++q) {
-        const double* S = (const double*)(smem + s * Cfg::STAGE_STRIDE) + soff;
-        mbar_wait(&full[s], ph);
-        double2 cc[RY];
-        double xl[RY], xr[RY];
-        const double2 up = *(const double2*)(S - ROW);
-        const double2 dn = *(const double2*)(S + RY * ROW);
-#pragma unroll
-        for (int r = 0; r < RY; ++r) {
-            cc[r] = *(const double2*)(S + r * ROW);
-            xl[r] = S[r * ROW - 1];
-            xr[r] = S[r * ROW + 2];
-        }
+    // Ring bookkeeping.  Stage s is read at iteration q (s = q % STAGES) and handed back through empty[s]
+    // (one arrival per warp).  The refill runs ONE iteration behind and rotates over the warps: at iteration q,
+    // warp (q % NWARP) waits - almost never actually - for empty[stage of q-1] and issues the TMA load of plane
+    // q-1+STAGES into it.  Nobody spins on a stage that is still being read, and the bookkeeping is two
+    // instructions per warp per plane for everyone else.
+    uint32_t s = 0, ph = 0;            // stage / full-barrier parity of the current iteration
+    uint32_t sp_prev = 0, ph_prev = 0; // stage / empty-barrier parity of the previous iteration
+    auto stage_ptr = [&]() { return (const double*)(smem + s * Cfg::STAGE_STRIDE) + soff; };
+    auto release_stage = [&](int q) {
         __syncwarp();
-        if (lane == 0) {
-            const uint32_t old = smem_arrive_count(&drained[s]);
-            if (old % NWARP == NWARP - 1 && q + STAGES < niter) {      // last reader refills the stage
-                mbar_arrive_expect_tx(&full[s], Cfg::STAGE_BYTES);
-                tma_load_3d(smem + s * Cfg::STAGE_STRIDE, &tmap, &full[s], bx, by, zs - 1 + q + STAGES);
+        if (lane == 0) mbar_arrive(&empty[s]);
+        if (q >= 1 && ((q - warp) & (NWARP - 1)) == 0 && q - 1 + STAGES < niter) {
+            if (lane == 0) {
+                mbar_wait(&empty[sp_prev], ph_prev);
+                mbar_arrive_expect_tx(&full[sp_prev], Cfg::STAGE_BYTES);
+                tma_load_3d(smem + sp_prev * Cfg::STAGE_STRIDE, &tmap, &full[sp_prev], bx, by, zs - 1 + q - 1 + STAGES);
             }
         }
-        __syncwarp();
-
-#pragma unroll
-        for (int r = 0; r < RY; ++r) {
-            const double2 ym = r == 0 ? up : cc[r - 1];
-            const double2 yp = r == RY - 1 ? dn : cc[r + 1];
-            double2 tn;
-            tn.x = partial_xy<ARITH>(cc[r].x, xl[r], cc[r].y, ym.x, yp.x, g.Dx, g.Dy);
-            tn.y = partial_xy<ARITH>(cc[r].y, cc[r].x, xr[r], ym.y, yp.y, g.Dx, g.Dy);
-            if (q >= 2) {
-                double2 o;
-                o.x = finish_z<ARITH>(t1[r].x, c1[r].x, c2[r].x, cc[r].x, g.Dz);
-                o.y = finish_z<ARITH>(t1[r].y, c1[r].y, c2[r].y, cc[r].y, g.Dz);
-                const int y = gy + r;
-                if (y >= 1 && y <= g.ny - 2) {
-                    double* o_ptr = out + (long long)r * g.pitch;
-                    if (vx0 && vx1) {
-                        *(double2*)o_ptr = o;
-                        if (RES) rmax = fmax(rmax, fmax(fabs(__dsub_rn(o.x, c1[r].x)), fabs(__dsub_rn(o.y, c1[r].y))));
-                    } else if (vx0) {
-                        o_ptr[0] = o.x;
-                        if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o.x, c1[r].x)));
-                    } else if (vx1) {
-                        o_ptr[1] = o.y;
-                        if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o.y, c1[r].y)));
-                    }
-                }
-            }
-            c2[r] = c1[r];
-            c1[r] = cc[r];
-            t1[r] = tn;
-        }
-        if (q >= 1) out += g.plane;
+        sp_prev = s;
+        ph_prev = ph;
         if (++s == STAGES) { s = 0; ph ^= 1u; }
+    };
+
+    // q = 0: plane zs-1, only its centre values are needed
+    {
+        const double* S = stage_ptr();
+        mbar_wait(&full[s], ph);
+#pragma unroll
+        for (int r = 0; r < RY; ++r) C[0][r] = *(const double2*)(S + r * ROW);
+        release_stage(0);
+    }
+    // q = 1: plane zs, centre + partial
+    {
+        const double* S = stage_ptr();
+        mbar_wait(&full[s], ph);
+        plane_update<RY, ARITH, RES, false>(S, ROW, C[1], C[0], C[0], t, tw, out, g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
+        release_stage(1);
+    }
+    // q >= 2: plane p = zs-1+q arrives -> finish plane p-1 (index q-2 of the chunk) and form partial(p)
+    int q = 2;
+    for (; q + 2 < niter; q += 3) {
+        {
+            const double* S = stage_ptr();
+            mbar_wait(&full[s], ph);
+            plane_update<RY, ARITH, RES, true>(S, ROW, C[2], C[1], C[0], t, tw, out, g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
+            release_stage(q);
+            out += g.plane;
+        }
+        {
+            const double* S = stage_ptr();
+            mbar_wait(&full[s], ph);
+            plane_update<RY, ARITH, RES, true>(S, ROW, C[0], C[2], C[1], t, tw, out, g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
+            release_stage(q + 1);
+            out += g.plane;
+        }
+        {
+            const double* S = stage_ptr();
+            mbar_wait(&full[s], ph);
+            plane_update<RY, ARITH, RES, true>(S, ROW, C[1], C[0], C[2], t, tw, out, g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
+            release_stage(q + 2);
+            out += g.plane;
+        }
+    }
+    if (q < niter) {
+        const double* S = stage_ptr();
+        mbar_wait(&full[s], ph);
+        plane_update<RY, ARITH, RES, true>(S, ROW, C[2], C[1], C[0], t, tw, out, g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
+        release_stage(q);
+        out += g.plane;
+        ++q;
+        if (q < niter) {
+            const double* S2 = stage_ptr();
+            mbar_wait(&full[s], ph);
+            plane_update<RY, ARITH, RES, true>(S2, ROW, C[0], C[2], C[1], t, tw, out, g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
+            release_stage(q);
+        }
     }
     if (RES) warp_residual_commit(rmax, res_slot);
 }

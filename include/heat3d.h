@@ -105,7 +105,8 @@ int heat3d_create(const heat3d_params* p, heat3d_ctx** out);
 /* Replaces cu:708-716.  Frees everything; NULL is accepted. */
 int heat3d_destroy(heat3d_ctx* ctx);
 
-/* 128-byte NCCL bootstrap id (process 0 calls this and ships the bytes to the others by any means —
+/* 128-byte NCCL bootstrap id, good for ONE heat3d_create per process (process 0 calls this and ships the bytes
+ * to the others by any means —
  * the reference used MPI_Init/MPI_Cart_create for the same purpose, cu:203-263). */
 int heat3d_nccl_unique_id(void* out128);
 

@@ -5,6 +5,7 @@
 // There is no CPU path in this file: every entry point needs a CUDA device and says so when there is none.
 #include "../../include/heat3d.h"
 #include "kernels.cuh"
+#include "internal.h"
 
 #include <cfloat>
 #include <cstdarg>
@@ -573,6 +574,15 @@ int copy_planes(Slab& s, int b, uint32_t nx, uint32_t ny, uint32_t zl, uint32_t 
 }
 
 }  // namespace
+
+int h3::set_last_error(int code, const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
 
 // =========================================================================================================
 extern "C" {

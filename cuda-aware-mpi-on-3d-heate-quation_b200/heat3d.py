@@ -62,6 +62,8 @@ EXPORTS = {
                              C.POINTER(C.c_int32), C.POINTER(C.c_uint32)]),
     "heat3d_residual": (C.c_int, [_ctx, _dp]),
     "heat3d_mean_abs_error_vs_y": (C.c_int, [_ctx, C.c_double, _dp]),
+    "heat3d_mean_abs_error_vs_y_noalloc": (C.c_int, [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_double,
+                                                     C.c_void_p, C.c_void_p]),
     "heat3d_snapshot_async": (C.c_int, [_ctx, _dp]),
     "heat3d_snapshot_wait": (C.c_int, [_ctx]),
     "heat3d_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
@@ -274,6 +276,15 @@ class Heat3D:
 
     def compute_stream(self, i=0):
         return lib().heat3d_compute_stream(self._ctx, i)
+
+
+NOALLOC_MAX_PLANES = 8192
+
+
+def mean_abs_error_vs_y_noalloc(d_field_ptr, nx, ny, nz, pitch_doubles, sp_y, d_err_ptr, stream=None):
+    """heat3d_mean_abs_error_vs_y_noalloc on the caller's own device buffers (raw addresses); queues work on
+    `stream` and returns - synchronise before reading d_err.  Allocates nothing; see include/heat3d.h for the limits."""
+    _check(lib().heat3d_mean_abs_error_vs_y_noalloc(d_field_ptr, nx, ny, nz, pitch_doubles, sp_y, d_err_ptr, stream))
 
 
 def slab_bounds(nz, nslabs):

@@ -156,6 +156,18 @@ int heat3d_residual(heat3d_ctx* ctx, double* residual);
  * ~1e-15 relative, not bitwise.  In a multi-process run every process gets the global mean. */
 int heat3d_mean_abs_error_vs_y(heat3d_ctx* ctx, double sp_y, double* err);
 
+/* The same quantity for callers that may not allocate device memory (no counterpart in the reference; added for
+ * hosts whose device memory is wholly owned by their own pool/allocator, or that cannot tolerate cudaMalloc's
+ * implicit synchronisation).  Works on the CALLER's buffers on the current device: d_field = nz planes of ny rows
+ * of pitch_doubles doubles (x fastest, plane 0 first), d_err = one double; both device pointers.  Launches on
+ * `stream` (a cudaStream_t, NULL = default stream) and returns without waiting.  Scratch lives in a fixed array
+ * inside the library: at most HEAT3D_NOALLOC_MAX_PLANES interior planes (nz - 2), larger fields are refused;
+ * calls that overlap on one GPU race on that array, so serialise them; the first call on each device resolves the
+ * array's address and should happen outside stream capture.  Never calls cudaMalloc/cudaFree. */
+#define HEAT3D_NOALLOC_MAX_PLANES 8192
+int heat3d_mean_abs_error_vs_y_noalloc(const double* d_field, uint32_t nx, uint32_t ny, uint32_t nz, uint32_t pitch_doubles,
+                                       double sp_y, double* d_err, void* stream);
+
 /* ---- snapshots, sync, diagnostics --------------------------------------------------------------------- */
 
 /* Asynchronous copy of the current time level into PINNED host memory (global layout; own planes only) on a

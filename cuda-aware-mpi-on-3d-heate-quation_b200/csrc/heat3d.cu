@@ -5,6 +5,7 @@
 // There is no CPU path in this file: every entry point needs a CUDA device and says so when there is none.
 #include "../../include/heat3d.h"
 #include "kernels.cuh"
+#include "kernels_t2.cuh"
 #include "internal.h"
 
 #include <cfloat>
@@ -148,6 +149,46 @@ const std::vector<TmaVariant>& variants()
     return v;
 }
 
+// ---- depth-2 temporal-blocking kernel variants --------------------------------------------------------
+struct T2Variant {
+    const char* name;
+    int cx, cy, ry, stages, minb;
+    size_t smem;
+    int threads;
+    const void* fn[2][2];   // [arith][res]
+};
+
+template <int CX, int CY, int RY, int ST, int MINB>
+T2Variant make_t2(const char* name)
+{
+    T2Variant v;
+    v.name = name;
+    v.cx = CX; v.cy = CY; v.ry = RY; v.stages = ST; v.minb = MINB;
+    v.smem = h3::Tma2Cfg<CX, CY, ST>::SMEM_BYTES;
+    v.threads = (CX / 2) * (CY / RY);
+    v.fn[0][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, false, MINB>;
+    v.fn[0][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, true, MINB>;
+    v.fn[1][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, false, MINB>;
+    v.fn[1][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, true, MINB>;
+    return v;
+}
+
+// compute region cx x cy (output tile (cx-4) x (cy-2)), rows/thread, stages, CTAs/SM.  First = default;
+// HEAT3D_T2_TUNE="cx,cy,ry,stages,ctas[,chunk_len]" selects another (experiments).
+const std::vector<T2Variant>& t2_variants()
+{
+    static const std::vector<T2Variant> v = {
+        make_t2<64, 32, 2, 4, 1>("t2_64x32_r2_s4_c1"),
+        make_t2<64, 32, 2, 3, 1>("t2_64x32_r2_s3_c1"),
+        make_t2<64, 16, 2, 4, 2>("t2_64x16_r2_s4_c2"),
+        make_t2<64, 16, 2, 3, 2>("t2_64x16_r2_s3_c2"),
+        make_t2<128, 16, 2, 4, 1>("t2_128x16_r2_s4_c1"),
+        make_t2<128, 16, 2, 3, 1>("t2_128x16_r2_s3_c1"),
+        make_t2<128, 8, 2, 4, 2>("t2_128x8_r2_s4_c2"),
+    };
+    return v;
+}
+
 struct Slab {
     int dev = 0;
     int gidx = 0;                 // global slab index
@@ -159,6 +200,7 @@ struct Slab {
     long long plane = 0;          // doubles per plane
     double* buf[2] = {nullptr, nullptr};
     CUtensorMap tmap[2];
+    CUtensorMap tmap2[2];         // depth-2 kernel's box shape
     cudaStream_t compute = nullptr, comm = nullptr, copy = nullptr;
     bool own_compute = true;
     cudaEvent_t ev_boundary = nullptr, ev_put = nullptr, ev_start = nullptr, ev_stop = nullptr, ev_snap = nullptr,
@@ -183,6 +225,8 @@ struct heat3d_ctx {
     std::vector<Slab> slabs;
     int cur = 0;                       // buffer holding the current time level
     const TmaVariant* variant = nullptr;
+    const T2Variant* variant2 = nullptr;   // set when temporal_k >= 2
+    int t2_chunk = 32;
     bool use_tma = true;
     bool multi_process = false;
     int snap_buf = -1;                 // buffer an async snapshot is still reading, or -1
@@ -202,18 +246,17 @@ int set_dev(const Slab& s)
     return HEAT3D_OK;
 }
 
-int make_tmap(Slab& s, int which, const heat3d_ctx* c)
+int make_tmap(Slab& s, CUtensorMap* map, int which, const heat3d_ctx* c, int box_x, int box_y)
 {
-    const TmaVariant& v = *c->variant;
     cuuint64_t dims[3] = {c->p.nx, c->p.ny, s.planes};
     cuuint64_t strides[2] = {(cuuint64_t)s.pitch * 8, (cuuint64_t)s.plane * 8};
-    cuuint32_t box[3] = {(cuuint32_t)(v.tx + 4), (cuuint32_t)(v.ty + 2), 1};
+    cuuint32_t box[3] = {(cuuint32_t)box_x, (cuuint32_t)box_y, 1};
     cuuint32_t estr[3] = {1, 1, 1};
     // L2 promotion widens every L2 miss to 128/256 B; the staged rows start 16 B before a 128-B boundary, so
     // promotion would drag in whole extra lines per row.  Default: none.  (HEAT3D_TMA_L2PROMO=0..3 for experiments.)
     CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_NONE;
     if (const char* e = getenv("HEAT3D_TMA_L2PROMO")) promo = (CUtensorMapL2promotion)atoi(e);
-    CUresult r = g_encode(&s.tmap[which], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, s.buf[which], dims, strides, box, estr,
+    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, s.buf[which], dims, strides, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
     return HEAT3D_OK;
@@ -265,6 +308,36 @@ int launch_stencil(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res)
 #undef H3_LAUNCH_BASE
         CU_TRY(cudaGetLastError());
     }
+    c->tm.launches++;
+    c->tm.last_call_launches++;
+    c->tm.last_call_stencil_launches++;
+    return HEAT3D_OK;
+}
+
+// One depth-2 launch: local output planes [za, zb) of slab s advance by TWO updates, reading buffer `src`.
+int launch_stencil_t2(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res)
+{
+    if (zb <= za) return HEAT3D_OK;
+    const T2Variant& v = *c->variant2;
+    h3::Geom g;
+    g.nx = (int)c->p.nx; g.ny = (int)c->p.ny; g.pitch = (int)s.pitch; g.plane = s.plane;
+    g.za = za; g.zb = zb; g.Dx = c->p.Dx; g.Dy = c->p.Dy; g.Dz = c->p.Dz;
+    const int ar = c->p.arith == HEAT3D_ARITH_FMA ? 1 : 0;
+    double* dst = s.buf[src ^ 1];
+    h3::TmaWork w;
+    w.ntx = ((int)c->p.nx + (v.cx - 4) - 1) / (v.cx - 4);
+    w.nty = ((int)c->p.ny + (v.cy - 2) - 1) / (v.cy - 2);
+    const int nzp = zb - za;
+    const long long ntiles = (long long)w.ntx * w.nty, slots = (long long)s.num_sms * v.minb;
+    long long nch = (nzp + c->t2_chunk - 1) / c->t2_chunk;
+    if (nch * ntiles < slots) nch = (slots + ntiles - 1) / ntiles;
+    if (nch > nzp) nch = nzp;
+    w.chunk_len = (int)((nzp + nch - 1) / nch);
+    w.nchunks = (nzp + w.chunk_len - 1) / w.chunk_len;
+    const long long grid = ntiles * w.nchunks;
+    int z1lo = (int)(1 - s.zg0), z1hi = (int)((long long)c->p.nz - 1 - s.zg0);   // level-1 planes that are global interior planes
+    void* args[] = {(void*)&s.tmap2[src], (void*)&dst, (void*)&g, (void*)&w, (void*)&z1lo, (void*)&z1hi, (void*)&s.d_res};
+    CU_TRY(cudaLaunchKernel(v.fn[ar][res ? 1 : 0], dim3((unsigned)grid), dim3(v.threads), args, v.smem, s.compute));
     c->tm.launches++;
     c->tm.last_call_launches++;
     c->tm.last_call_stencil_launches++;
@@ -344,8 +417,12 @@ int wait_ghosts(heat3d_ctx* c, Slab& s)
     return HEAT3D_OK;
 }
 
-int step_once(heat3d_ctx* c, bool res)
+// One pass over HBM advancing every slab by k updates (k = 1, or 2 when the context was created with temporal_k >= 2).
+int step_block(heat3d_ctx* c, int k, bool res)
 {
+    auto launch = [&](Slab& s, int src, int za, int zb, bool r) {
+        return k == 2 ? launch_stencil_t2(c, s, src, za, zb, r) : launch_stencil(c, s, src, za, zb, r);
+    };
     const int src = c->cur, dst = c->cur ^ 1;
     const bool overlap = !(c->p.flags & HEAT3D_FLAG_NO_OVERLAP);
     for (Slab& s : c->slabs) {
@@ -354,7 +431,7 @@ int step_once(heat3d_ctx* c, bool res)
         if (c->snap_buf == dst) CU_TRY(cudaStreamWaitEvent(s.compute, s.ev_snap, 0));
         if (res) CU_TRY(cudaMemsetAsync(s.d_res, 0, sizeof(unsigned long long), s.compute));
         if (!s.lower && !s.upper) {
-            if ((rc = launch_stencil(c, s, src, s.za, s.zb, res))) return rc;
+            if ((rc = launch(s, src, s.za, s.zb, res))) return rc;
             continue;
         }
         if (c->halo_timed) CU_TRY(cudaEventRecord(s.ev_wait0[c->call_steps % HALO_RING], s.compute));
@@ -367,10 +444,10 @@ int step_once(heat3d_ctx* c, bool res)
         if (lo_end > s.zb) lo_end = s.zb;
         if (hi_beg < lo_end) hi_beg = lo_end;
         if (!overlap) { lo_end = s.za; hi_beg = s.zb; }
-        if ((rc = launch_stencil(c, s, src, s.za, lo_end, res))) return rc;
-        if ((rc = launch_stencil(c, s, src, hi_beg, s.zb, res))) return rc;
+        if ((rc = launch(s, src, s.za, lo_end, res))) return rc;
+        if ((rc = launch(s, src, hi_beg, s.zb, res))) return rc;
         if (overlap) CU_TRY(cudaEventRecord(s.ev_boundary, s.compute));
-        if ((rc = launch_stencil(c, s, src, lo_end, hi_beg, res))) return rc;
+        if ((rc = launch(s, src, lo_end, hi_beg, res))) return rc;
         if (!overlap) CU_TRY(cudaEventRecord(s.ev_boundary, s.compute));
     }
     if (c->snap_buf == dst) c->snap_buf = -1;
@@ -379,7 +456,7 @@ int step_once(heat3d_ctx* c, bool res)
         if (rc) return rc;
     }
     c->cur = dst;
-    c->tm.steps++;
+    c->tm.steps += k;
     c->call_steps++;
     return HEAT3D_OK;
 }
@@ -540,12 +617,20 @@ int setup_slab(heat3d_ctx* c, Slab& s)
     s.lower = s.gidx > 0;
     s.upper = s.gidx < p.nslabs - 1;
     if (c->use_tma) {
-        for (int w = 0; w < 2; ++w)
-            if ((rc = make_tmap(s, w, c))) return rc;
         const TmaVariant& v = *c->variant;
+        for (int w = 0; w < 2; ++w)
+            if ((rc = make_tmap(s, &s.tmap[w], w, c, v.tx + 4, v.ty + 2))) return rc;
         for (int ar = 0; ar < 2; ++ar)
             for (int r = 0; r < 2; ++r)
                 CU_TRY(cudaFuncSetAttribute(v.fn[ar][r], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v.smem));
+        if (c->variant2) {
+            const T2Variant& v2 = *c->variant2;
+            for (int w = 0; w < 2; ++w)
+                if ((rc = make_tmap(s, &s.tmap2[w], w, c, v2.cx + 4, v2.cy + 2))) return rc;
+            for (int ar = 0; ar < 2; ++ar)
+                for (int r = 0; r < 2; ++r)
+                    CU_TRY(cudaFuncSetAttribute(v2.fn[ar][r], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v2.smem));
+        }
     }
     return HEAT3D_OK;
 }
@@ -623,7 +708,8 @@ int heat3d_create(const heat3d_params* pin, heat3d_ctx** out)
     if (p.nx > (1u << 30) || p.ny > (1u << 30) || p.nz > (1u << 30)) return fail(HEAT3D_ERR_INVALID, "grid axis too large");
     if (p.arith != HEAT3D_ARITH_STRICT && p.arith != HEAT3D_ARITH_FMA) return fail(HEAT3D_ERR_INVALID, "unknown arith %d", p.arith);
     if (p.temporal_k <= 0) p.temporal_k = 1;
-    if (p.temporal_k != 1) return fail(HEAT3D_ERR_INVALID, "temporal_k=%d not available in this build (only 1)", p.temporal_k);
+    if (p.temporal_k > 2) return fail(HEAT3D_ERR_INVALID, "temporal_k=%d not available in this build (1 or 2)", p.temporal_k);
+    if (p.temporal_k == 2 && p.kernel == HEAT3D_KERNEL_BASELINE) return fail(HEAT3D_ERR_INVALID, "temporal_k=2 needs the TMA kernels");
     if (p.nslabs <= 0) p.nslabs = 1;
     if (p.nlocal <= 0) p.nlocal = p.nslabs;
     if (p.slab_first < 0 || p.slab_first + p.nlocal > p.nslabs) return fail(HEAT3D_ERR_INVALID, "slab range [%d,%d) outside [0,%d)", p.slab_first, p.slab_first + p.nlocal, p.nslabs);
@@ -664,6 +750,20 @@ int heat3d_create(const heat3d_params* pin, heat3d_ctx** out)
                 if ((!p.tune[0] || p.tune[0] == v.tx) && (!p.tune[1] || p.tune[1] == v.ty) && (!p.tune[2] || p.tune[2] == v.ry) &&
                     (!p.tune[3] || p.tune[3] == v.stages) && (!p.tune[4] || p.tune[4] == v.minb)) { c->variant = &v; break; }
             if (!c->variant) { delete c; return fail(HEAT3D_ERR_INVALID, "no TMA kernel variant matches tune={%d,%d,%d,%d,%d}", p.tune[0], p.tune[1], p.tune[2], p.tune[3], p.tune[4]); }
+        }
+    }
+
+    if (c->use_tma && p.temporal_k == 2) {
+        const auto& vs = t2_variants();
+        c->variant2 = &vs[0];
+        if (const char* e = getenv("HEAT3D_T2_TUNE")) {
+            int t[6] = {0, 0, 0, 0, 0, 0};
+            sscanf(e, "%d,%d,%d,%d,%d,%d", &t[0], &t[1], &t[2], &t[3], &t[4], &t[5]);
+            c->variant2 = nullptr;
+            for (const T2Variant& v : vs)
+                if (t[0] == v.cx && t[1] == v.cy && t[2] == v.ry && t[3] == v.stages && t[4] == v.minb) { c->variant2 = &v; break; }
+            if (!c->variant2) { delete c; return fail(HEAT3D_ERR_INVALID, "no depth-2 kernel variant matches HEAT3D_T2_TUNE=%s", e); }
+            if (t[5] > 0) c->t2_chunk = t[5];
         }
     }
 
@@ -744,6 +844,7 @@ int heat3d_layout(const heat3d_ctx* c, int32_t i, uint32_t* pitch, uint32_t* pla
 const char* heat3d_kernel_name(const heat3d_ctx* c)
 {
     if (!c) return "";
+    if (c->variant2) return c->variant2->name;
     return c->use_tma ? c->variant->name : "baseline_64x4";
 }
 
@@ -856,8 +957,11 @@ int heat3d_step(heat3d_ctx* c, uint32_t nsteps)
     int rc = check_ctx(c);
     if (rc) return rc;
     if ((rc = begin_call(c))) return rc;
-    for (uint32_t i = 0; i < nsteps; ++i)
-        if ((rc = step_once(c, false))) return rc;
+    uint32_t left = nsteps;
+    for (; c->variant2 && left >= 2; left -= 2)
+        if ((rc = step_block(c, 2, false))) return rc;
+    for (; left; --left)
+        if ((rc = step_block(c, 1, false))) return rc;
     if (nsteps) c->have_res = false;
     return end_call(c);
 }
@@ -869,9 +973,15 @@ int heat3d_step_residual(heat3d_ctx* c, uint32_t nsteps, double* residual)
     if (!residual) return fail(HEAT3D_ERR_INVALID, "null residual pointer");
     if (nsteps == 0) return fail(HEAT3D_ERR_INVALID, "nsteps must be >= 1 to produce a residual");
     if ((rc = begin_call(c))) return rc;
-    for (uint32_t i = 0; i + 1 < nsteps; ++i)
-        if ((rc = step_once(c, false))) return rc;
-    if ((rc = step_once(c, true))) return rc;
+    // all but the last block plain; the last block (2 updates if that leaves an even count, else 1) carries the residual
+    uint32_t left = nsteps;
+    const uint32_t last = (c->variant2 && left >= 2 && left % 2 == 0) ? 2u : 1u;
+    left -= last;
+    for (; c->variant2 && left >= 2; left -= 2)
+        if ((rc = step_block(c, 2, false))) return rc;
+    for (; left; --left)
+        if ((rc = step_block(c, 1, false))) return rc;
+    if ((rc = step_block(c, (int)last, true))) return rc;
     if ((rc = end_call(c))) return rc;
     return fetch_residual(c, residual);
 }

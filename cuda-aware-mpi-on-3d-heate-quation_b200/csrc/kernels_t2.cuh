@@ -1,0 +1,235 @@
+// Temporal blocking, depth 2: two FTCS updates per trip through HBM.
+//
+// Same z-streaming skeleton as stencil_tma_kernel (kernels.cuh), with a second stencil level stacked on the
+// first inside the CTA:
+//   level 0  planes of time n arrive by TMA, box (CX+4) x (CY+2), exactly as in the depth-1 kernel;
+//   level 1  every thread finishes its 2 x RY patch of the time n+1 plane over the whole CX x CY compute region
+//            (Dirichlet cells and Dirichlet planes are carried over unchanged, as the reference never updates
+//            them), keeps the centre values in registers and publishes the plane to a double-buffered shared
+//            "mid" plane;
+//   level 2  after one CTA barrier each thread reads the xy neighbours of its level-1 cells from the mid plane
+//            and finishes the time n+2 plane over the inner (CX-4) x (CY-2) region, which is what goes to HBM.
+// Each level uses the split partial_xy / finish_z evaluation, so every cell sees exactly the operations, in
+// exactly the order, of two separate depth-1 sweeps: results are bit-identical to stepping twice.
+// HBM traffic is one read + one write per cell per TWO updates (8 B per cell-update); the price is the
+// redundant level-1 ring (CX*CY / ((CX-4)*(CY-2)) of the level-1 work) and one barrier per plane.  The barrier
+// also tells the refill thread that the stage just read is free, so this kernel needs no empty barriers.
+#pragma once
+#include "kernels.cuh"
+
+namespace h3 {
+
+template <int CX, int CY, int STAGES>
+struct Tma2Cfg {
+    static constexpr int OX = CX - 4, OY = CY - 2;                    // output tile
+    static constexpr int ROW = CX + 4;
+    static constexpr int ROWS = CY + 2;
+    static constexpr int STAGE_BYTES = ROW * ROWS * 8;
+    static constexpr int STAGE_STRIDE = (STAGE_BYTES + 127) / 128 * 128;
+    static constexpr int SMEM_BYTES = (STAGES + 2) * STAGE_STRIDE + STAGES * 8;   // stages | 2 mid planes | full barriers
+};
+
+// Per-thread constants of the two levels.
+struct T2Plan {
+    bool all1;            // every cell of the patch is a domain-interior cell (level 1 needs no carry-over select)
+    bool i1x0, i1x1;      // column interior?
+    uint32_t rows1;       // bit r: row interior?
+    StorePlan st;         // level-2 stores: inside the CTA's output tile AND domain-interior
+};
+
+// finish plane p-1 of one level (-> o) and start plane p (t, tw) from its centre values cn and xy neighbours
+template <int RY, int ARITH, bool FINISH, bool PARTIAL>
+__device__ __forceinline__ void level_step(const double2 (&cn)[RY], const double (&xl)[RY], const double (&xr)[RY], const double2& up,
+                                           const double2& dn, const double2 (&cp2)[RY], double2 (&t)[RY], double2 (&tw)[RY],
+                                           double2 (&o)[RY], double Dx, double Dy, double Dz)
+{
+#pragma unroll
+    for (int r = 0; r < RY; ++r) {
+        if (FINISH) {
+            o[r].x = finish_z2<ARITH>(t[r].x, tw[r].x, cp2[r].x, cn[r].x, Dz);
+            o[r].y = finish_z2<ARITH>(t[r].y, tw[r].y, cp2[r].y, cn[r].y, Dz);
+        }
+        if (PARTIAL) {
+            const double2 ym = r == 0 ? up : cn[r - 1];
+            const double2 yp = r == RY - 1 ? dn : cn[r + 1];
+            tw[r].x = twice(cn[r].x);
+            tw[r].y = twice(cn[r].y);
+            t[r].x = partial_xy2<ARITH>(cn[r].x, tw[r].x, xl[r], cn[r].y, ym.x, yp.x, Dx, Dy);
+            t[r].y = partial_xy2<ARITH>(cn[r].y, tw[r].y, cn[r].x, xr[r], ym.y, yp.y, Dx, Dy);
+        }
+    }
+}
+
+template <int RY>
+__device__ __forceinline__ void load_neighbours(const double* __restrict__ S, int row_pitch, double (&xl)[RY], double (&xr)[RY],
+                                                double2& up, double2& dn)
+{
+    up = *(const double2*)(S - row_pitch);
+    dn = *(const double2*)(S + RY * row_pitch);
+#pragma unroll
+    for (int r = 0; r < RY; ++r) {
+        xl[r] = S[r * row_pitch - 1];
+        xr[r] = S[r * row_pitch + 2];
+    }
+}
+
+template <int CX, int CY, int RY, int STAGES, int ARITH, bool RES, int MINB>
+__global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
+    stencil_tma_t2_kernel(const __grid_constant__ CUtensorMap tmap, double* __restrict__ dst, Geom g, TmaWork w, int z1lo, int z1hi,
+                          unsigned long long* res_slot)
+{
+    using Cfg = Tma2Cfg<CX, CY, STAGES>;
+    constexpr int NTHR = (CX / 2) * (CY / RY);
+    constexpr int NWARP = NTHR / 32;
+    constexpr int ROW = Cfg::ROW;
+    static_assert(CX % 64 == 0 && CY % RY == 0 && NTHR % 32 == 0 && NTHR <= 1024 && STAGES >= 2, "tile shape");
+
+    extern __shared__ __align__(128) unsigned char smem[];
+    unsigned char* mid = smem + STAGES * Cfg::STAGE_STRIDE;
+    uint64_t* full = (uint64_t*)(smem + (STAGES + 2) * Cfg::STAGE_STRIDE);
+
+    const int tid = threadIdx.x;
+    const int ntiles = w.ntx * w.nty;
+    const int tile = blockIdx.x % ntiles;
+    const int chunk = blockIdx.x / ntiles;
+    const int zs = g.za + chunk * w.chunk_len;                  // first output (time n+2) plane of this CTA
+    const int cnt = min(w.chunk_len, g.zb - zs);
+    if (cnt <= 0) return;
+    const int niter = cnt + 4;                                  // input planes zs-2 .. zs+cnt+1
+    const int ox = (tile % w.ntx) * Cfg::OX, oy = (tile / w.ntx) * Cfg::OY;   // output tile origin
+    const int bx = ox - 4, by = oy - 2;                         // TMA box origin
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s)
+            if (s < niter) {
+                mbar_arrive_expect_tx(&full[s], Cfg::STAGE_BYTES);
+                tma_load_3d(smem + s * Cfg::STAGE_STRIDE, &tmap, &full[s], bx, by, zs - 2 + s);
+            }
+    }
+    __syncthreads();
+
+    const int lx = tid % (CX / 2);
+    const int ry = tid / (CX / 2);
+    const int warp = tid >> 5, lane = tid & 31;
+    const int gx = ox - 2 + 2 * lx;                             // global x of this thread's first cell
+    const int gy = oy - 1 + ry * RY;                            // global y of this thread's first row
+    T2Plan pl;
+    pl.i1x0 = gx >= 1 && gx <= g.nx - 2;
+    pl.i1x1 = gx + 1 >= 1 && gx + 1 <= g.nx - 2;
+    pl.rows1 = 0;
+    pl.st.rows = 0;
+#pragma unroll
+    for (int r = 0; r < RY; ++r) {
+        const bool in = gy + r >= 1 && gy + r <= g.ny - 2;
+        const int cyi = ry * RY + r;
+        if (in) pl.rows1 |= 1u << r;
+        if (in && cyi >= 1 && cyi <= CY - 2) pl.st.rows |= 1u << r;
+    }
+    pl.all1 = pl.i1x0 && pl.i1x1 && pl.rows1 == (1u << RY) - 1u;
+    const bool xin = lx >= 1 && lx <= CX / 2 - 2;
+    pl.st.x0 = xin && pl.i1x0;
+    pl.st.x1 = xin && pl.i1x1;
+    pl.st.all = pl.st.x0 && pl.st.x1 && pl.st.rows == (1u << RY) - 1u;
+    double* out = dst + (long long)zs * g.plane + (long long)gy * g.pitch + gx;
+    const int soff = (1 + ry * RY) * ROW + 2 + 2 * lx;
+    double rmax = 0.0;
+
+    double2 C0[3][RY], t0[RY], tw0[RY];      // level 0: centres of the last three planes, partial / 2*centre of the newest
+    double2 C1[3][RY], t1[RY], tw1[RY];      // level 1: same
+#pragma unroll
+    for (int r = 0; r < RY; ++r) t0[r] = tw0[r] = t1[r] = tw1[r] = C1[0][r] = C1[1][r] = C1[2][r] = make_double2(0.0, 0.0);
+
+    uint32_t s = 0, ph = 0;
+    int par = 0;
+
+    // One input plane.  q = index of the plane inside the chunk's input run; the level-1 plane finished here is
+    // local plane zs + q - 3, the level-2 plane finished here is zs + q - 4.
+    auto body = [&](int q, double2 (&c0n)[RY], const double2 (&c0p1)[RY], const double2 (&c0p2)[RY], double2 (&c1n)[RY],
+                    const double2 (&c1p1)[RY], const double2 (&c1p2)[RY]) {
+        const double* S = (const double*)(smem + s * Cfg::STAGE_STRIDE) + soff;
+        mbar_wait(&full[s], ph);
+        double xl[RY], xr[RY];
+        double2 up, dn;
+#pragma unroll
+        for (int r = 0; r < RY; ++r) c0n[r] = *(const double2*)(S + r * ROW);
+        load_neighbours<RY>(S, ROW, xl, xr, up, dn);
+
+        // ---- level 1: finish plane q-1 of the input run, start plane q
+        if (q >= 2) level_step<RY, ARITH, true, true>(c0n, xl, xr, up, dn, c0p2, t0, tw0, c1n, g.Dx, g.Dy, g.Dz);
+        else if (q == 1) level_step<RY, ARITH, false, true>(c0n, xl, xr, up, dn, c0p2, t0, tw0, c1n, g.Dx, g.Dy, g.Dz);
+        if (q >= 2) {
+            const int z1 = zs + q - 3;
+            const bool zint = z1 >= z1lo && z1 < z1hi;
+            if (!(zint && pl.all1)) {           // Dirichlet cells / planes keep their value
+#pragma unroll
+                for (int r = 0; r < RY; ++r) {
+                    const bool row = zint && ((pl.rows1 >> r) & 1u);
+                    if (!(row && pl.i1x0)) c1n[r].x = c0p1[r].x;
+                    if (!(row && pl.i1x1)) c1n[r].y = c0p1[r].y;
+                }
+            }
+            double* M = (double*)(mid + par * Cfg::STAGE_STRIDE) + soff;
+#pragma unroll
+            for (int r = 0; r < RY; ++r) *(double2*)(M + r * ROW) = c1n[r];
+        }
+        __syncthreads();        // the stage has been read by everyone; the mid plane is complete
+        if (warp == (q & (NWARP - 1)) && lane == 0 && q + STAGES < niter) {
+            mbar_arrive_expect_tx(&full[s], Cfg::STAGE_BYTES);
+            tma_load_3d(smem + s * Cfg::STAGE_STRIDE, &tmap, &full[s], bx, by, zs - 2 + q + STAGES);
+        }
+        if (++s == STAGES) { s = 0; ph ^= 1u; }
+
+        // ---- level 2: finish plane (zs+q-4), start plane (zs+q-3)
+        if (q >= 3) {
+            const double* M = (const double*)(mid + par * Cfg::STAGE_STRIDE) + soff;
+            load_neighbours<RY>(M, ROW, xl, xr, up, dn);
+            double2 o[RY];
+            if (q >= 4) level_step<RY, ARITH, true, true>(c1n, xl, xr, up, dn, c1p2, t1, tw1, o, g.Dx, g.Dy, g.Dz);
+            else level_step<RY, ARITH, false, true>(c1n, xl, xr, up, dn, c1p2, t1, tw1, o, g.Dx, g.Dy, g.Dz);
+            if (q >= 4) {
+#pragma unroll
+                for (int r = 0; r < RY; ++r) {
+                    double* o_ptr = out + (long long)r * g.pitch;
+                    if (pl.st.all) {
+                        *(double2*)o_ptr = o[r];
+                        if (RES) rmax = fmax(rmax, fmax(fabs(__dsub_rn(o[r].x, c1p1[r].x)), fabs(__dsub_rn(o[r].y, c1p1[r].y))));
+                    } else if ((pl.st.rows >> r) & 1u) {
+                        if (pl.st.x0) {
+                            o_ptr[0] = o[r].x;
+                            if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o[r].x, c1p1[r].x)));
+                        }
+                        if (pl.st.x1) {
+                            o_ptr[1] = o[r].y;
+                            if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o[r].y, c1p1[r].y)));
+                        }
+                    }
+                }
+                out += g.plane;
+            }
+        }
+        par ^= 1;
+    };
+
+    // Register rotation: level 0 newest = C0[q % 3]; level 1 newest (plane q-1 of the run) = C1[(q + 2) % 3].
+    body(0, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
+    body(1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
+    body(2, C0[2], C0[1], C0[0], C1[1], C1[0], C1[2]);
+    int q = 3;
+    for (; q + 2 < niter; q += 3) {
+        body(q, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
+        body(q + 1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
+        body(q + 2, C0[2], C0[1], C0[0], C1[1], C1[0], C1[2]);
+    }
+    if (q < niter) {
+        body(q, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
+        if (q + 1 < niter) body(q + 1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
+    }
+    if (RES) warp_residual_commit(rmax, res_slot);
+}
+
+}  // namespace h3

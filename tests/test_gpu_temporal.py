@@ -1,0 +1,129 @@
+"""GPU: temporal blocking (temporal_k=2: two FTCS updates per HBM pass) must be bit-identical to stepping twice.
+
+Same bar as tests/test_gpu_parity.py: strict arithmetic bit-exact against the CPU oracle (np.array_equal), fma
+arithmetic bit-exact against the oracle's fma ordering."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+T2_TUNES = ["64,32,2,4,1", "64,32,2,3,1", "64,16,2,4,2", "64,16,2,3,2", "128,16,2,4,1", "128,16,2,3,1", "128,8,2,4,2"]
+
+
+@pytest.fixture(scope="module")
+def h3():
+    import __graft_entry__ as ge
+    return ge.load_package()
+
+
+@pytest.fixture(autouse=True)
+def _clean_env():
+    os.environ.pop("HEAT3D_T2_TUNE", None)
+    yield
+    os.environ.pop("HEAT3D_T2_TUNE", None)
+
+
+def _oracle_field(oracle, nx, ny, nz, nsteps, arith=0):
+    _, _, D = oracle.coefficients(nx, ny, nz)
+    return oracle.steps(oracle.init_field(nx, ny, nz), D, nsteps, arith=arith, threads=8)
+
+
+@pytest.mark.parametrize("shape,nsteps", [((27, 27, 27), 40), ((33, 17, 65), 25), ((64, 64, 64), 30), ((5, 4, 3), 7), ((3, 3, 3), 4),
+                                          ((130, 35, 9), 12), ((257, 66, 20), 9), ((3, 200, 40), 6), ((61, 31, 4), 2), ((125, 64, 37), 1)])
+def test_depth2_bit_exact_vs_oracle(h3, oracle, shape, nsteps):
+    nx, ny, nz = shape
+    ref = _oracle_field(oracle, nx, ny, nz, nsteps)
+    with h3.Heat3D(nx, ny, nz, temporal_k=2) as sim:
+        assert sim.kernel_name().startswith("t2_")
+        assert sim.layout()[2] == 2                   # ghost depth follows the temporal depth
+        sim.init_reference_field()
+        sim.step(nsteps)
+        got = sim.download()
+        assert sim.timing()["steps"] == nsteps
+    assert np.array_equal(got, ref)
+
+
+@pytest.mark.parametrize("tune", T2_TUNES)
+def test_every_depth2_variant(h3, oracle, tune):
+    nx, ny, nz, nsteps = 150, 70, 41, 10
+    os.environ["HEAT3D_T2_TUNE"] = tune + ",7"        # short chunks: several chunk seams inside the grid
+    ref = _oracle_field(oracle, nx, ny, nz, nsteps)
+    prev = _oracle_field(oracle, nx, ny, nz, nsteps - 1)
+    with h3.Heat3D(nx, ny, nz, temporal_k=2) as sim:
+        assert sim.kernel_name() == "t2_%sx%s_r%s_s%s_c%s" % tuple(tune.split(","))
+        sim.init_reference_field()
+        res = sim.step_residual(nsteps)               # even count: the residual comes out of the depth-2 kernel
+        got = sim.download()
+    assert np.array_equal(got, ref)
+    assert res == oracle.residual(ref, prev)
+
+
+def test_depth2_residual_odd_and_even(h3, oracle):
+    nx, ny, nz = 48, 40, 33
+    for nsteps in (1, 2, 3, 8, 9):
+        ref = _oracle_field(oracle, nx, ny, nz, nsteps)
+        prev = _oracle_field(oracle, nx, ny, nz, nsteps - 1)
+        with h3.Heat3D(nx, ny, nz, temporal_k=2) as sim:
+            sim.init_reference_field()
+            res = sim.step_residual(nsteps)
+            got = sim.download()
+        assert np.array_equal(got, ref), nsteps
+        assert res == oracle.residual(ref, prev), nsteps
+
+
+def test_depth2_fma_mode(h3, oracle):
+    nx, ny, nz, nsteps = 48, 40, 33, 100
+    with h3.Heat3D(nx, ny, nz, temporal_k=2, arith=h3.ARITH_FMA) as sim:
+        sim.init_reference_field()
+        sim.step(nsteps)
+        got = sim.download()
+    assert np.array_equal(got, _oracle_field(oracle, nx, ny, nz, nsteps, arith=1))
+    assert np.max(np.abs(got - _oracle_field(oracle, nx, ny, nz, nsteps))) <= 1e-12
+
+
+def test_depth2_random_field_and_convergence_run(h3, oracle, manifest, golden_field):
+    nx, ny, nz = 45, 31, 22
+    T = np.random.default_rng(7).random((nz, ny, nx))
+    _, _, D = oracle.coefficients(nx, ny, nz)
+    with h3.Heat3D(nx, ny, nz, temporal_k=2) as sim:
+        sim.upload(T)
+        sim.step(6)
+        assert np.array_equal(sim.download(), oracle.steps(T.copy(), D, 6))
+    # the reference's convergence run, residual examined every 2nd iteration so the depth-2 kernel does the work
+    nx, ny, nz, it, eps = manifest["c27_converge"]["args"]
+    with h3.Heat3D(nx, ny, nz, temporal_k=2) as sim:
+        sim.init_reference_field()
+        applied, fin, conv = sim.run(it, float(eps), check_every=2)
+        got = sim.download()
+    assert conv and fin in (3302, 3303) and applied == fin + 1
+    assert np.array_equal(got, _oracle_field(oracle, nx, ny, nz, applied))
+
+
+@pytest.mark.parametrize("shape,P,nsteps", [((40, 24, 31), 2, 20), ((21, 13, 30), 4, 25), ((70, 40, 17), 3, 13), ((33, 17, 16), 8, 6)])
+def test_depth2_multi_slab_equals_single_domain_bitwise(h3, oracle, shape, P, nsteps):
+    nx, ny, nz = shape
+    ref = _oracle_field(oracle, nx, ny, nz, nsteps)
+    prev = _oracle_field(oracle, nx, ny, nz, nsteps - 1)
+    for flags in (0, h3.FLAG_NO_OVERLAP):
+        with h3.Heat3D(nx, ny, nz, temporal_k=2, nslabs=P, devices=[0] * P, flags=flags) as sim:
+            sim.init_reference_field()
+            res = sim.step_residual(nsteps)
+            got = sim.download()
+        assert np.array_equal(got, ref), flags
+        assert res == oracle.residual(ref, prev)
+
+
+def test_depth2_large_grid_matches_depth1(h3):
+    """512^3: the depth-2 path against the depth-1 path of the same library, bit for bit, after an odd step count."""
+    n, nsteps = 512, 21
+    with h3.Heat3D(n, n, n) as a:
+        a.init_reference_field()
+        a.step(nsteps)
+        A = a.download()
+    with h3.Heat3D(n, n, n, temporal_k=2) as b:
+        b.init_reference_field()
+        b.step(nsteps)
+        B = b.download()
+    assert np.array_equal(A, B)

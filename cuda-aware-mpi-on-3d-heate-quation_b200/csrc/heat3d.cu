@@ -42,7 +42,7 @@ int fail(int code, const char* fmt, ...)
 typedef struct ncclComm* ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 enum { ncclSuccess = 0 };
-enum { ncclFloat64 = 8 };
+enum { ncclInt8 = 0, ncclFloat64 = 8 };
 enum { ncclMax = 2, ncclSum = 0 };
 struct NcclApi {
     void* handle = nullptr;
@@ -52,6 +52,7 @@ struct NcclApi {
     int (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*Recv)(void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*GroupStart)() = nullptr;
     int (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
@@ -73,6 +74,7 @@ int load_nccl()
     H3_SYM(Send, "ncclSend")
     H3_SYM(Recv, "ncclRecv")
     H3_SYM(AllReduce, "ncclAllReduce")
+    H3_SYM(AllGather, "ncclAllGather")
     H3_SYM(GroupStart, "ncclGroupStart")
     H3_SYM(GroupEnd, "ncclGroupEnd")
     H3_SYM(GetErrorString, "ncclGetErrorString")
@@ -102,6 +104,25 @@ int load_encode()
     CU_TRY(cudaGetDriverEntryPointByVersion("cuTensorMapEncodeTiled", &fn, 12000, cudaEnableDefault, &q));
     if (q != cudaDriverEntryPointSuccess || !fn) return fail(HEAT3D_ERR_CUDA, "driver lacks cuTensorMapEncodeTiled");
     g_encode = (EncodeTiledFn)fn;
+    return HEAT3D_OK;
+}
+
+// ---- stream memory operations (flag writes / waits ordered in a stream, no kernel involved) ---------------
+typedef CUresult (*StreamValue64Fn)(CUstream, CUdeviceptr, cuuint64_t, unsigned int);
+StreamValue64Fn g_stream_write64 = nullptr, g_stream_wait64 = nullptr;
+
+int load_stream_memops()
+{
+    if (g_stream_write64 && g_stream_wait64) return HEAT3D_OK;
+    void* fw = nullptr;
+    void* fa = nullptr;
+    cudaDriverEntryPointQueryResult q1, q2;
+    CU_TRY(cudaGetDriverEntryPointByVersion("cuStreamWriteValue64", &fw, 12000, cudaEnableDefault, &q1));
+    CU_TRY(cudaGetDriverEntryPointByVersion("cuStreamWaitValue64", &fa, 12000, cudaEnableDefault, &q2));
+    if (q1 != cudaDriverEntryPointSuccess || q2 != cudaDriverEntryPointSuccess || !fw || !fa)
+        return fail(HEAT3D_ERR_CUDA, "driver lacks cuStreamWriteValue64/cuStreamWaitValue64");
+    g_stream_write64 = (StreamValue64Fn)fw;
+    g_stream_wait64 = (StreamValue64Fn)fa;
     return HEAT3D_OK;
 }
 
@@ -178,10 +199,10 @@ T2Variant make_t2(const char* name)
 const std::vector<T2Variant>& t2_variants()
 {
     static const std::vector<T2Variant> v = {
+        make_t2<64, 16, 2, 3, 2>("t2_64x16_r2_s3_c2"),
+        make_t2<64, 16, 2, 4, 2>("t2_64x16_r2_s4_c2"),
         make_t2<64, 32, 2, 4, 1>("t2_64x32_r2_s4_c1"),
         make_t2<64, 32, 2, 3, 1>("t2_64x32_r2_s3_c1"),
-        make_t2<64, 16, 2, 4, 2>("t2_64x16_r2_s4_c2"),
-        make_t2<64, 16, 2, 3, 2>("t2_64x16_r2_s3_c2"),
         make_t2<128, 16, 2, 4, 1>("t2_128x16_r2_s4_c1"),
         make_t2<128, 16, 2, 3, 1>("t2_128x16_r2_s3_c1"),
         make_t2<128, 8, 2, 4, 2>("t2_128x8_r2_s4_c2"),
@@ -213,6 +234,12 @@ struct Slab {
     int partial_blocks = 0;
     int num_sms = 0;
     ncclComm_t nccl = nullptr;
+    // cross-process neighbours reached through CUDA IPC (side 0 = lower, 1 = upper): their two field buffers and
+    // their arrival flags mapped into this process, plus this slab's own flags {written by lower, written by upper}
+    bool ipc = false;
+    double* peer_buf[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+    unsigned long long* peer_flags[2] = {nullptr, nullptr};
+    unsigned long long* d_flags = nullptr;
     bool lower = false, upper = false;     // has a neighbouring slab below / above
     int za = 0, zb = 0;                    // local output plane range (owned ∩ global interior)
 };
@@ -226,7 +253,7 @@ struct heat3d_ctx {
     int cur = 0;                       // buffer holding the current time level
     const TmaVariant* variant = nullptr;
     const T2Variant* variant2 = nullptr;   // set when temporal_k >= 2
-    int t2_chunk = 32;
+    int t2_chunk = 64;
     bool use_tma = true;
     bool multi_process = false;
     int snap_buf = -1;                 // buffer an async snapshot is still reading, or -1
@@ -234,6 +261,7 @@ struct heat3d_ctx {
     double last_res = 0.0;
     heat3d_timing tm;
     bool halo_timed = false;
+    unsigned long long seq = 0;        // number of ghost exchanges issued so far (same on every process)
     bool timing_pending = false;       // a call's ev_start/ev_stop have not been folded into tm yet
     uint32_t call_steps = 0;           // steps issued by the current/last call
 };
@@ -378,7 +406,29 @@ int exchange_ghosts(heat3d_ctx* c, int b)
             } else any_nccl = true;
         }
     }
-    if (any_nccl) {
+    c->seq++;
+    if (any_nccl && c->slabs[0].ipc) {
+        // one-sided puts into the neighbour process's ghost planes by the copy engines, then a flag write that is
+        // ordered after the copy in the stream: no SM is needed while the interior kernel owns them all
+        for (Slab& s : c->slabs) {
+            int rc = set_dev(s);
+            if (rc) return rc;
+            const size_t bytes = (size_t)s.G * s.plane * sizeof(double);
+            const uint32_t nzl = s.z1 - s.z0;
+            if (s.lower && !local_slab(c, s.gidx - 1)) {      // my first G owned planes -> lower neighbour's upper ghost
+                const uint32_t n_nzl = (uint32_t)((uint64_t)s.gidx * c->p.nz / c->p.nslabs) - (uint32_t)((uint64_t)(s.gidx - 1) * c->p.nz / c->p.nslabs);
+                CU_TRY(cudaMemcpyAsync(s.peer_buf[0][b] + (long long)(s.G + n_nzl) * s.plane, s.buf[b] + (long long)s.G * s.plane, bytes,
+                                       cudaMemcpyDeviceToDevice, s.comm));
+                CUresult r = g_stream_write64((CUstream)s.comm, (CUdeviceptr)(s.peer_flags[0] + 1), c->seq, 0);
+                if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuStreamWriteValue64 failed with CUresult %d", (int)r);
+            }
+            if (s.upper && !local_slab(c, s.gidx + 1)) {      // my last G owned planes -> upper neighbour's lower ghost
+                CU_TRY(cudaMemcpyAsync(s.peer_buf[1][b], s.buf[b] + (long long)nzl * s.plane, bytes, cudaMemcpyDeviceToDevice, s.comm));
+                CUresult r = g_stream_write64((CUstream)s.comm, (CUdeviceptr)(s.peer_flags[1] + 0), c->seq, 0);
+                if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuStreamWriteValue64 failed with CUresult %d", (int)r);
+            }
+        }
+    } else if (any_nccl) {
         NCCL_TRY(g_nccl.GroupStart());
         for (Slab& s : c->slabs) {
             const size_t cnt = (size_t)s.G * s.plane;
@@ -406,13 +456,22 @@ int exchange_ghosts(heat3d_ctx* c, int b)
 // Make slab s's compute stream wait until its ghost planes (filled by the previous exchange) have landed.
 int wait_ghosts(heat3d_ctx* c, Slab& s)
 {
+    // own ev_put: my previous sends have left my planes; neighbour's ev_put / flag: its planes have landed in my ghosts
     if (s.lower) {
         Slab* n = local_slab(c, s.gidx - 1);
         CU_TRY(cudaStreamWaitEvent(s.compute, n ? n->ev_put : s.ev_put, 0));
+        if (!n && s.ipc && c->seq) {
+            CUresult r = g_stream_wait64((CUstream)s.compute, (CUdeviceptr)(s.d_flags + 0), c->seq, CU_STREAM_WAIT_VALUE_GEQ);
+            if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuStreamWaitValue64 failed with CUresult %d", (int)r);
+        }
     }
     if (s.upper) {
         Slab* n = local_slab(c, s.gidx + 1);
         CU_TRY(cudaStreamWaitEvent(s.compute, n ? n->ev_put : s.ev_put, 0));
+        if (!n && s.ipc && c->seq) {
+            CUresult r = g_stream_wait64((CUstream)s.compute, (CUdeviceptr)(s.d_flags + 1), c->seq, CU_STREAM_WAIT_VALUE_GEQ);
+            if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuStreamWaitValue64 failed with CUresult %d", (int)r);
+        }
     }
     return HEAT3D_OK;
 }
@@ -547,6 +606,12 @@ int finish_timing(heat3d_ctx* c)
 void destroy_slab(Slab& s)
 {
     cudaSetDevice(s.dev);
+    for (int side = 0; side < 2; ++side) {
+        for (int b = 0; b < 2; ++b)
+            if (s.peer_buf[side][b]) cudaIpcCloseMemHandle(s.peer_buf[side][b]);
+        if (s.peer_flags[side]) cudaIpcCloseMemHandle(s.peer_flags[side]);
+    }
+    if (s.d_flags) cudaFree(s.d_flags);
     if (s.nccl && g_nccl.CommDestroy) g_nccl.CommDestroy(s.nccl);
     for (int b = 0; b < 2; ++b)
         if (s.buf[b]) cudaFree(s.buf[b]);
@@ -586,7 +651,11 @@ int setup_slab(heat3d_ctx* c, Slab& s)
     }
     if (p.stream && c->slabs.size() == 1) { s.compute = (cudaStream_t)p.stream; s.own_compute = false; }
     else CU_TRY(cudaStreamCreateWithFlags(&s.compute, cudaStreamNonBlocking));
-    CU_TRY(cudaStreamCreateWithFlags(&s.comm, cudaStreamNonBlocking));
+    {   // the exchange must not queue behind the interior kernel's CTAs: give its stream the highest priority
+        int lo = 0, hi = 0;
+        CU_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CU_TRY(cudaStreamCreateWithPriority(&s.comm, cudaStreamNonBlocking, hi));
+    }
     CU_TRY(cudaStreamCreateWithFlags(&s.copy, cudaStreamNonBlocking));
     cudaEvent_t* sync_evs[] = {&s.ev_boundary, &s.ev_put, &s.ev_snap, &s.ev_tmp};
     for (cudaEvent_t* e : sync_evs) CU_TRY(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
@@ -632,6 +701,70 @@ int setup_slab(heat3d_ctx* c, Slab& s)
                     CU_TRY(cudaFuncSetAttribute(v2.fn[ar][r], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v2.smem));
         }
     }
+    return HEAT3D_OK;
+}
+
+// Cross-process neighbours: map their field buffers and arrival flags into this process (CUDA IPC), so ghost planes
+// move by copy-engine puts + stream-ordered flag writes instead of NCCL kernels that would have to queue for SMs
+// behind the interior stencil.  Handles travel by one ncclAllGather.  Every process must reach the same verdict,
+// so the per-process outcome is all-reduced (min) before the path is switched on; on any failure the NCCL
+// send/recv path stays in use.
+int setup_ipc(heat3d_ctx* c, bool want)
+{
+    Slab& s = c->slabs[0];
+    int rc = set_dev(s);
+    if (rc) return rc;
+    struct Handles { cudaIpcMemHandle_t buf[2], flags; };
+    const int P = c->p.nslabs;
+    bool ok = want && load_stream_memops() == HEAT3D_OK;
+    CU_TRY(cudaMalloc(&s.d_flags, 2 * sizeof(unsigned long long)));
+    CU_TRY(cudaMemset(s.d_flags, 0, 2 * sizeof(unsigned long long)));
+    Handles mine;
+    memset(&mine, 0, sizeof mine);
+    if (ok) {
+        ok = cudaIpcGetMemHandle(&mine.buf[0], s.buf[0]) == cudaSuccess && cudaIpcGetMemHandle(&mine.buf[1], s.buf[1]) == cudaSuccess &&
+             cudaIpcGetMemHandle(&mine.flags, s.d_flags) == cudaSuccess;
+        cudaGetLastError();
+    }
+    unsigned char* d_all = nullptr;
+    CU_TRY(cudaMalloc(&d_all, (size_t)(P + 1) * sizeof(Handles)));
+    CU_TRY(cudaMemcpy(d_all + (size_t)P * sizeof(Handles), &mine, sizeof mine, cudaMemcpyHostToDevice));
+    NCCL_TRY(g_nccl.AllGather(d_all + (size_t)P * sizeof(Handles), d_all, sizeof(Handles), ncclInt8, s.nccl, s.comm));
+    CU_TRY(cudaStreamSynchronize(s.comm));
+    std::vector<Handles> all(P);
+    CU_TRY(cudaMemcpy(all.data(), d_all, (size_t)P * sizeof(Handles), cudaMemcpyDeviceToHost));
+    if (ok) {
+        for (int side = 0; side < 2 && ok; ++side) {
+            const int n = s.gidx + (side == 0 ? -1 : 1);
+            if (n < 0 || n >= P) continue;
+            for (int b = 0; b < 2 && ok; ++b)
+                ok = cudaIpcOpenMemHandle((void**)&s.peer_buf[side][b], all[n].buf[b], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+            if (ok) ok = cudaIpcOpenMemHandle((void**)&s.peer_flags[side], all[n].flags, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+        }
+        cudaGetLastError();
+    }
+    // agree: IPC only if it worked everywhere
+    double verdict = ok ? 1.0 : 0.0;
+    CU_TRY(cudaMemcpy(s.d_scalar, &verdict, sizeof verdict, cudaMemcpyHostToDevice));
+    NCCL_TRY(g_nccl.AllReduce(s.d_scalar, s.d_scalar + 1, 1, ncclFloat64, 3 /* ncclMin */, s.nccl, s.comm));
+    CU_TRY(cudaMemcpyAsync(&verdict, s.d_scalar + 1, sizeof verdict, cudaMemcpyDeviceToHost, s.comm));
+    CU_TRY(cudaStreamSynchronize(s.comm));
+    CU_TRY(cudaFree(d_all));
+    s.ipc = verdict > 0.5;
+    return HEAT3D_OK;
+}
+
+// Multi-process contexts: every process has finished all work it queued so far (its puts into neighbours included).
+int mp_barrier(heat3d_ctx* c)
+{
+    if (!c->multi_process) return HEAT3D_OK;
+    Slab& s = c->slabs[0];
+    int rc = set_dev(s);
+    if (rc) return rc;
+    CU_TRY(cudaStreamSynchronize(s.compute));
+    CU_TRY(cudaStreamSynchronize(s.comm));
+    NCCL_TRY(g_nccl.AllReduce(s.d_scalar, s.d_scalar + 1, 1, ncclFloat64, ncclSum, s.nccl, s.comm));
+    CU_TRY(cudaStreamSynchronize(s.comm));
     return HEAT3D_OK;
 }
 
@@ -803,6 +936,9 @@ int heat3d_create(const heat3d_params* pin, heat3d_ctx** out)
         }
         if (r == ncclSuccess) r = g_nccl.GroupEnd();
         if (r != ncclSuccess) { fail(HEAT3D_ERR_NCCL, "ncclCommInitRank failed: %s", g_nccl.GetErrorString(r)); heat3d_destroy(c); return HEAT3D_ERR_NCCL; }
+        const char* ex = getenv("HEAT3D_EXCHANGE");
+        const bool want_ipc = !(ex && strcmp(ex, "nccl") == 0);
+        if ((rc = setup_ipc(c, want_ipc))) { heat3d_destroy(c); return rc; }
     }
     cudaSetDevice(c->slabs[0].dev);
     *out = c;
@@ -815,6 +951,12 @@ int heat3d_destroy(heat3d_ctx* c)
     for (Slab& s : c->slabs) {
         cudaSetDevice(s.dev);
         cudaDeviceSynchronize();
+    }
+    // neighbours may still be putting into this process's ghost planes: nobody frees until everybody has drained
+    if (c->multi_process && !c->slabs.empty() && c->slabs[0].nccl && c->slabs[0].d_scalar) {
+        Slab& s = c->slabs[0];
+        cudaSetDevice(s.dev);
+        if (g_nccl.AllReduce(s.d_scalar, s.d_scalar + 1, 1, ncclFloat64, ncclSum, s.nccl, s.comm) == ncclSuccess) cudaStreamSynchronize(s.comm);
     }
     for (Slab& s : c->slabs) destroy_slab(s);
     delete c;
@@ -848,6 +990,13 @@ const char* heat3d_kernel_name(const heat3d_ctx* c)
     return c->use_tma ? c->variant->name : "baseline_64x4";
 }
 
+const char* heat3d_exchange_name(const heat3d_ctx* c)
+{
+    if (!c) return "";
+    if (c->multi_process) return c->slabs[0].ipc ? "ipc-put" : "nccl";
+    return c->slabs.size() > 1 ? "peer-copy" : "none";
+}
+
 void* heat3d_compute_stream(heat3d_ctx* c, int32_t i)
 {
     if (!c || i < 0 || i >= (int)c->slabs.size()) return nullptr;
@@ -872,6 +1021,7 @@ int heat3d_init_reference_field(heat3d_ctx* c, double sp_y)
     int rc = check_ctx(c);
     if (rc) return rc;
     if ((rc = heat3d_sync(c))) return rc;
+    if ((rc = mp_barrier(c))) return rc;      // no neighbour may still be writing into the ghosts this call rewrites
     for (Slab& s : c->slabs) {
         if ((rc = set_dev(s))) return rc;
         h3::init_reference_field_kernel<<<s.num_sms * 8, 256, 0, s.compute>>>(s.buf[0], s.buf[1], (int)c->p.nx, (int)c->p.ny, (int)s.pitch,
@@ -894,6 +1044,7 @@ int heat3d_upload_planes(heat3d_ctx* c, const double* host, uint32_t z0, uint32_
     if (z0 < c->slabs.front().z0 || z0 + n > c->slabs.back().z1)
         return fail(HEAT3D_ERR_INVALID, "planes [%u,%u) outside this context's range [%u,%u)", z0, z0 + n, c->slabs.front().z0, c->slabs.back().z1);
     if ((rc = heat3d_sync(c))) return rc;
+    if ((rc = mp_barrier(c))) return rc;
     const size_t plane_host = (size_t)c->p.nx * c->p.ny;
     for (Slab& s : c->slabs) {
         const uint32_t a = z0 > s.z0 ? z0 : s.z0, b = (z0 + n) < s.z1 ? (z0 + n) : s.z1;

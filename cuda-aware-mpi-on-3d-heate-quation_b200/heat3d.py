@@ -76,6 +76,7 @@ EXPORTS = {
     "heat3d_last_error": (C.c_char_p, []),
     "heat3d_version": (C.c_int, []),
     "heat3d_kernel_name": (C.c_char_p, [_ctx]),
+    "heat3d_exchange_name": (C.c_char_p, [_ctx]),
 }
 
 _lib = None
@@ -273,6 +274,9 @@ class Heat3D:
 
     def kernel_name(self):
         return lib().heat3d_kernel_name(self._ctx).decode()
+
+    def exchange_name(self):
+        return lib().heat3d_exchange_name(self._ctx).decode()
 
     def compute_stream(self, i=0):
         return lib().heat3d_compute_stream(self._ctx, i)

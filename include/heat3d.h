@@ -25,8 +25,11 @@
  * (slab s owns global planes [s*nz/nslabs, (s+1)*nz/nslabs)), each carrying `temporal_k` ghost planes
  * per side.  A context owns `nlocal` consecutive slabs starting at `slab_first`, one CUDA device per
  * slab (devices may repeat).  Slabs in one context exchange ghost planes by peer copies; slabs in
- * different processes by NCCL send/recv (then `nccl_unique_id` is required).  nslabs = nlocal = 1 is
- * the plain single-GPU case.
+ * different processes by copy-engine puts into CUDA-IPC-mapped ghost planes, or NCCL send/recv where IPC is not
+ * available (either way `nccl_unique_id` is required: NCCL carries the bootstrap and the scalar reductions).
+ * In a multi-process run heat3d_create, heat3d_init_reference_field, heat3d_upload*, heat3d_step_residual,
+ * heat3d_run, heat3d_mean_abs_error_vs_y and heat3d_destroy are collective: every process calls them, in the
+ * same order.  nslabs = nlocal = 1 is the plain single-GPU case.
  */
 #ifndef HEAT3D_H
 #define HEAT3D_H
@@ -197,6 +200,11 @@ int heat3d_version(void);
 
 /* Name of the stencil kernel variant the context dispatches to (static string). */
 const char* heat3d_kernel_name(const heat3d_ctx* ctx);
+
+/* How ghost planes travel in this context (static string): "none" (single slab), "peer-copy" (slabs of one process:
+ * cudaMemcpyPeerAsync), "ipc-put" (other processes: copy-engine puts into CUDA-IPC-mapped ghost planes + stream-ordered
+ * arrival flags; default) or "nccl" (ncclSend/ncclRecv; used when IPC is unavailable or HEAT3D_EXCHANGE=nccl is set). */
+const char* heat3d_exchange_name(const heat3d_ctx* ctx);
 
 #ifdef __cplusplus
 }

@@ -62,26 +62,31 @@ def main():
         local = int(os.environ.get("LOCAL_RANK", rank))
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        for kernel in (2, 1):
+        for kernel, tk, exchange in ((2, 1, "ipc-put"), (2, 2, "ipc-put"), (2, 2, "nccl"), (1, 1, "nccl")):
+            os.environ["HEAT3D_EXCHANGE"] = "nccl" if exchange == "nccl" else "ipc"
             box = [h3.nccl_unique_id() if rank == 0 else None]      # a bootstrap id serves ONE communicator
             dist.broadcast_object_list(box, src=0)
-            with h3.Heat3D(nx, ny, nz, kernel=kernel, nslabs=world, slab_first=rank, nlocal=1, devices=[local], nccl_id=box[0],
-                           flags=h3.FLAG_TIME_HALO) as sim:
+            with h3.Heat3D(nx, ny, nz, kernel=kernel, temporal_k=tk, nslabs=world, slab_first=rank, nlocal=1, devices=[local],
+                           nccl_id=box[0], flags=h3.FLAG_TIME_HALO) as sim:
                 assert sim.local_range() == (z0, z1)
+                assert sim.exchange_name() == exchange, (sim.exchange_name(), exchange)
                 sim.init_reference_field()
                 sim.step(nsteps - 1)
                 res = sim.step_residual(1)
                 got = sim.download_planes(z0, z1 - z0)
                 err = sim.mean_abs_error_vs_y()
-                assert np.array_equal(got, ref[z0:z1]), f"rank {rank} kernel {kernel}: slab differs from single domain"
+                assert np.array_equal(got, ref[z0:z1]), f"rank {rank} kernel {kernel} k {tk} {exchange}: slab differs from single domain"
                 assert res == oracle.residual(ref, ref_prev), (res, oracle.residual(ref, ref_prev))
                 exp = oracle.mean_abs_error_vs_y(ref)
                 assert abs(err - exp) < 1e-12, (err, exp, err - exp)   # serial sum (oracle) vs tree sum (device)
-                # upload path: random field, ghosts refreshed over NCCL
+                # upload path: random field, ghosts refreshed by the exchange; then re-init and run again
                 T = np.random.default_rng(5).random((nz, ny, nx))
                 sim.upload_planes(np.ascontiguousarray(T[z0:z1]), z0)
-                sim.step(4)
-                assert np.array_equal(sim.download_planes(z0, z1 - z0), oracle.steps(T.copy(), D, 4)[z0:z1])
+                sim.step(5)
+                assert np.array_equal(sim.download_planes(z0, z1 - z0), oracle.steps(T.copy(), D, 5)[z0:z1])
+                sim.init_reference_field()
+                sim.step(nsteps)
+                assert np.array_equal(sim.download_planes(z0, z1 - z0), ref[z0:z1])
             dist.barrier()
     dist.barrier()
     dist.destroy_process_group()

@@ -60,16 +60,27 @@ __device__ __forceinline__ void level_step(const double2 (&cn)[RY], const double
     }
 }
 
-template <int RY>
-__device__ __forceinline__ void load_neighbours(const double* __restrict__ S, int row_pitch, double (&xl)[RY], double (&xr)[RY],
-                                                double2& up, double2& dn)
+// xy neighbours of a thread's 2 x RY patch, read from the staged plane.  SHFL = take the x neighbours from the
+// adjacent lanes' registers by warp shuffle instead (edge lanes still read the halo column): the kernel is bound
+// by shared-memory wavefronts (ncu: l1tex 80 %), and a strided 8-byte load costs 4 wavefronts per warp, but the four
+// 32-bit shuffles per row it takes to replace them turned out slower on B200 (profiles/r01_sweep_k2_shfl.txt).
+template <int RY, bool SHFL>
+__device__ __forceinline__ void load_neighbours(const double* __restrict__ S, int row_pitch, const double2 (&cn)[RY], int lane,
+                                                double (&xl)[RY], double (&xr)[RY], double2& up, double2& dn)
 {
     up = *(const double2*)(S - row_pitch);
     dn = *(const double2*)(S + RY * row_pitch);
 #pragma unroll
     for (int r = 0; r < RY; ++r) {
-        xl[r] = S[r * row_pitch - 1];
-        xr[r] = S[r * row_pitch + 2];
+        if (SHFL) {
+            xl[r] = __shfl_up_sync(0xffffffffu, cn[r].y, 1);
+            xr[r] = __shfl_down_sync(0xffffffffu, cn[r].x, 1);
+            if (lane == 0) xl[r] = S[r * row_pitch - 1];
+            if (lane == 31) xr[r] = S[r * row_pitch + 2];
+        } else {
+            xl[r] = S[r * row_pitch - 1];
+            xr[r] = S[r * row_pitch + 2];
+        }
     }
 }
 
@@ -82,6 +93,11 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     constexpr int NTHR = (CX / 2) * (CY / RY);
     constexpr int NWARP = NTHR / 32;
     constexpr int ROW = Cfg::ROW;
+#ifdef HEAT3D_T2_SHFL_X
+    constexpr bool SHFL_X = true;      // measured on B200: 433 GLUPS vs 536 with shared-memory loads - left off
+#else
+    constexpr bool SHFL_X = false;
+#endif
     static_assert(CX % 64 == 0 && CY % RY == 0 && NTHR % 32 == 0 && NTHR <= 1024 && STAGES >= 2, "tile shape");
 
     extern __shared__ __align__(128) unsigned char smem[];
@@ -157,7 +173,7 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
         double2 up, dn;
 #pragma unroll
         for (int r = 0; r < RY; ++r) c0n[r] = *(const double2*)(S + r * ROW);
-        load_neighbours<RY>(S, ROW, xl, xr, up, dn);
+        load_neighbours<RY, SHFL_X>(S, ROW, c0n, lane, xl, xr, up, dn);
 
         // ---- level 1: finish plane q-1 of the input run, start plane q
         if (q >= 2) level_step<RY, ARITH, true, true>(c0n, xl, xr, up, dn, c0p2, t0, tw0, c1n, g.Dx, g.Dy, g.Dz);
@@ -187,7 +203,7 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
         // ---- level 2: finish plane (zs+q-4), start plane (zs+q-3)
         if (q >= 3) {
             const double* M = (const double*)(mid + par * Cfg::STAGE_STRIDE) + soff;
-            load_neighbours<RY>(M, ROW, xl, xr, up, dn);
+            load_neighbours<RY, SHFL_X>(M, ROW, c1n, lane, xl, xr, up, dn);
             double2 o[RY];
             if (q >= 4) level_step<RY, ARITH, true, true>(c1n, xl, xr, up, dn, c1p2, t1, tw1, o, g.Dx, g.Dy, g.Dz);
             else level_step<RY, ARITH, false, true>(c1n, xl, xr, up, dn, c1p2, t1, tw1, o, g.Dx, g.Dy, g.Dz);

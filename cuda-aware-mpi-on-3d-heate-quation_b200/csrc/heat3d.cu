@@ -8,6 +8,7 @@
 #include "kernels_t2.cuh"
 #include "internal.h"
 
+#include <algorithm>
 #include <cfloat>
 #include <cstdarg>
 #include <cstdio>
@@ -240,6 +241,8 @@ struct Slab {
     double* peer_buf[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
     unsigned long long* peer_flags[2] = {nullptr, nullptr};
     unsigned long long* d_flags = nullptr;
+    unsigned long long* d_done = nullptr;    // end-chunk CTAs finished so far (device counter the exchange stream waits on)
+    unsigned long long done_target = 0;      // value d_done reaches when every end chunk launched so far is in memory
     bool lower = false, upper = false;     // has a neighbouring slab below / above
     int za = 0, zb = 0;                    // local output plane range (owned ∩ global interior)
 };
@@ -261,6 +264,7 @@ struct heat3d_ctx {
     double last_res = 0.0;
     heat3d_timing tm;
     bool halo_timed = false;
+    bool end_signal = false;           // stream memory operations available: single-launch steps with end-chunk signalling
     unsigned long long seq = 0;        // number of ghost exchanges issued so far (same on every process)
     bool timing_pending = false;       // a call's ev_start/ev_stop have not been folded into tm yet
     uint32_t call_steps = 0;           // steps issued by the current/last call
@@ -290,8 +294,44 @@ int make_tmap(Slab& s, CUtensorMap* map, int which, const heat3d_ctx* c, int box
     return HEAT3D_OK;
 }
 
+// Cuts output planes [za, zb) into an optional short end chunk per side whose neighbour is waiting (ends bit 0 =
+// lower, bit 1 = upper) plus uniform middle chunks; returns the grid size and books the end-chunk CTAs on the
+// slab's completion counter.
+long long plan_chunks(h3::TmaWork& w, int za, int zb, int ends, int end_len, int chunk_len, long long slots, Slab& s)
+{
+    const long long ntiles = (long long)w.ntx * w.nty;
+    w.n_end = 0;
+    w.mid_za = za;
+    w.mid_zb = zb;
+    w.done = ends ? s.d_done : nullptr;
+    for (int i = 0; i < 2; ++i) w.end_za[i] = w.end_zb[i] = 0;
+    if ((ends & 1) && w.mid_zb > w.mid_za) {
+        const int e = std::min(end_len, w.mid_zb - w.mid_za);
+        w.end_za[w.n_end] = w.mid_za; w.end_zb[w.n_end] = w.mid_za + e;
+        w.mid_za += e; w.n_end++;
+    }
+    if ((ends & 2) && w.mid_zb > w.mid_za) {
+        const int e = std::min(end_len, w.mid_zb - w.mid_za);
+        w.end_za[w.n_end] = w.mid_zb - e; w.end_zb[w.n_end] = w.mid_zb;
+        w.mid_zb -= e; w.n_end++;
+    }
+    const int nzp = w.mid_zb - w.mid_za;
+    long long nch = 0;
+    w.chunk_len = chunk_len;
+    if (nzp > 0) {
+        nch = (nzp + chunk_len - 1) / chunk_len;
+        if ((nch + w.n_end) * ntiles < slots) nch = (slots + ntiles - 1) / ntiles - w.n_end;
+        if (nch < 1) nch = 1;
+        if (nch > nzp) nch = nzp;
+        w.chunk_len = (int)((nzp + nch - 1) / nch);
+        nch = (nzp + w.chunk_len - 1) / w.chunk_len;
+    }
+    if (ends) s.done_target += (unsigned long long)ntiles * w.n_end;
+    return ntiles * (w.n_end + nch);
+}
+
 // One stencil launch over local output planes [za, zb) of slab s, reading buffer `src`.
-int launch_stencil(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res)
+int launch_stencil(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res, int ends = 0)
 {
     if (zb <= za) return HEAT3D_OK;
     h3::Geom g;
@@ -304,18 +344,11 @@ int launch_stencil(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res)
         h3::TmaWork w;
         w.ntx = ((int)c->p.nx + v.tx - 1) / v.tx;
         w.nty = ((int)c->p.ny + v.ty - 1) / v.ty;
-        const int nzp = zb - za;
-        const long long ntiles = (long long)w.ntx * w.nty, slots = (long long)s.num_sms * v.minb;
         // z-chunks: short chunks (default 16 output planes, tune[5] overrides) make the grid sweep the domain
         // z-major, wave after wave, so the planes a wave touches - and the halos its tiles share - stay in L2;
         // but never fewer chunks than it takes to fill every resident CTA slot once.
-        int clen = c->p.tune[5] > 0 ? c->p.tune[5] : 16;
-        long long nch = (nzp + clen - 1) / clen;
-        if (nch * ntiles < slots) nch = (slots + ntiles - 1) / ntiles;
-        if (nch > nzp) nch = nzp;
-        w.chunk_len = (int)((nzp + nch - 1) / nch);
-        w.nchunks = (nzp + w.chunk_len - 1) / w.chunk_len;
-        const long long grid = ntiles * w.nchunks;
+        const long long grid = plan_chunks(w, za, zb, ends, /*end_len=*/8, c->p.tune[5] > 0 ? c->p.tune[5] : 16,
+                                           (long long)s.num_sms * v.minb, s);
         void* args[] = {(void*)&s.tmap[src], (void*)&dst, (void*)&g, (void*)&w, (void*)&s.d_res};
         CU_TRY(cudaLaunchKernel(v.fn[ar][res ? 1 : 0], dim3((unsigned)grid), dim3(v.threads), args, v.smem, s.compute));
     } else {
@@ -343,7 +376,7 @@ int launch_stencil(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res)
 }
 
 // One depth-2 launch: local output planes [za, zb) of slab s advance by TWO updates, reading buffer `src`.
-int launch_stencil_t2(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res)
+int launch_stencil_t2(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res, int ends = 0)
 {
     if (zb <= za) return HEAT3D_OK;
     const T2Variant& v = *c->variant2;
@@ -355,14 +388,7 @@ int launch_stencil_t2(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res)
     h3::TmaWork w;
     w.ntx = ((int)c->p.nx + (v.cx - 4) - 1) / (v.cx - 4);
     w.nty = ((int)c->p.ny + (v.cy - 2) - 1) / (v.cy - 2);
-    const int nzp = zb - za;
-    const long long ntiles = (long long)w.ntx * w.nty, slots = (long long)s.num_sms * v.minb;
-    long long nch = (nzp + c->t2_chunk - 1) / c->t2_chunk;
-    if (nch * ntiles < slots) nch = (slots + ntiles - 1) / ntiles;
-    if (nch > nzp) nch = nzp;
-    w.chunk_len = (int)((nzp + nch - 1) / nch);
-    w.nchunks = (nzp + w.chunk_len - 1) / w.chunk_len;
-    const long long grid = ntiles * w.nchunks;
+    const long long grid = plan_chunks(w, za, zb, ends, /*end_len=*/16, c->t2_chunk, (long long)s.num_sms * v.minb, s);
     int z1lo = (int)(1 - s.zg0), z1hi = (int)((long long)c->p.nz - 1 - s.zg0);   // level-1 planes that are global interior planes
     void* args[] = {(void*)&s.tmap2[src], (void*)&dst, (void*)&g, (void*)&w, (void*)&z1lo, (void*)&z1hi, (void*)&s.d_res};
     CU_TRY(cudaLaunchKernel(v.fn[ar][res ? 1 : 0], dim3((unsigned)grid), dim3(v.threads), args, v.smem, s.compute));
@@ -381,14 +407,19 @@ Slab* local_slab(heat3d_ctx* c, int gidx)
 // Push the outermost G owned planes of buffer `b` into the neighbours' ghost planes of their buffer `b`
 // (same-process neighbours: peer copy; other processes: NCCL send/recv), on each slab's comm stream,
 // after that slab's ev_boundary.  Records ev_put per slab.
-int exchange_ghosts(heat3d_ctx* c, int b)
+int exchange_ghosts(heat3d_ctx* c, int b, bool after_counted_launch = false)
 {
     bool any_nccl = false;
     for (Slab& s : c->slabs) {
         if (!s.lower && !s.upper) continue;
         int rc = set_dev(s);
         if (rc) return rc;
-        CU_TRY(cudaStreamWaitEvent(s.comm, s.ev_boundary, 0));
+        if (after_counted_launch) {     // the end chunks of the launch just queued have counted themselves done
+            CUresult r = g_stream_wait64((CUstream)s.comm, (CUdeviceptr)s.d_done, s.done_target, CU_STREAM_WAIT_VALUE_GEQ);
+            if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuStreamWaitValue64 failed with CUresult %d", (int)r);
+        } else {
+            CU_TRY(cudaStreamWaitEvent(s.comm, s.ev_boundary, 0));
+        }
         const size_t bytes = (size_t)s.G * s.plane * sizeof(double);
         const uint32_t nzl = s.z1 - s.z0;
         if (s.lower) {
@@ -479,39 +510,48 @@ int wait_ghosts(heat3d_ctx* c, Slab& s)
 // One pass over HBM advancing every slab by k updates (k = 1, or 2 when the context was created with temporal_k >= 2).
 int step_block(heat3d_ctx* c, int k, bool res)
 {
-    auto launch = [&](Slab& s, int src, int za, int zb, bool r) {
-        return k == 2 ? launch_stencil_t2(c, s, src, za, zb, r) : launch_stencil(c, s, src, za, zb, r);
+    auto launch = [&](Slab& s, int src, int za, int zb, bool r, int ends) {
+        return k == 2 ? launch_stencil_t2(c, s, src, za, zb, r, ends) : launch_stencil(c, s, src, za, zb, r, ends);
     };
     const int src = c->cur, dst = c->cur ^ 1;
     const bool overlap = !(c->p.flags & HEAT3D_FLAG_NO_OVERLAP);
+    bool counted = false;
     for (Slab& s : c->slabs) {
         int rc = set_dev(s);
         if (rc) return rc;
         if (c->snap_buf == dst) CU_TRY(cudaStreamWaitEvent(s.compute, s.ev_snap, 0));
         if (res) CU_TRY(cudaMemsetAsync(s.d_res, 0, sizeof(unsigned long long), s.compute));
         if (!s.lower && !s.upper) {
-            if ((rc = launch(s, src, s.za, s.zb, res))) return rc;
+            if ((rc = launch(s, src, s.za, s.zb, res, 0))) return rc;
             continue;
         }
         if (c->halo_timed) CU_TRY(cudaEventRecord(s.ev_wait0[c->call_steps % HALO_RING], s.compute));
         if ((rc = wait_ghosts(c, s))) return rc;
         if (c->halo_timed) CU_TRY(cudaEventRecord(s.ev_wait1[c->call_steps % HALO_RING], s.compute));
-        // planes whose results the neighbours need first, then the rest while the exchange is in flight
+        if (overlap && c->use_tma && c->end_signal) {
+            // ONE launch: the chunks next to a neighbour run first and count themselves done on s.d_done; the exchange
+            // stream waits for that count, so the ghost planes leave while this kernel works on the rest of the slab
+            if ((rc = launch(s, src, s.za, s.zb, res, (s.lower ? 1 : 0) | (s.upper ? 2 : 0)))) return rc;
+            counted = true;
+            continue;
+        }
+        // fallback (no stream memory operations, or the baseline kernel): outer planes in launches of their own,
+        // an event after them, then the rest while the exchange is in flight
         const int G = (int)s.G;
         int lo_end = s.lower ? s.za + G : s.za;
         int hi_beg = s.upper ? s.zb - G : s.zb;
         if (lo_end > s.zb) lo_end = s.zb;
         if (hi_beg < lo_end) hi_beg = lo_end;
         if (!overlap) { lo_end = s.za; hi_beg = s.zb; }
-        if ((rc = launch(s, src, s.za, lo_end, res))) return rc;
-        if ((rc = launch(s, src, hi_beg, s.zb, res))) return rc;
+        if ((rc = launch(s, src, s.za, lo_end, res, 0))) return rc;
+        if ((rc = launch(s, src, hi_beg, s.zb, res, 0))) return rc;
         if (overlap) CU_TRY(cudaEventRecord(s.ev_boundary, s.compute));
-        if ((rc = launch(s, src, lo_end, hi_beg, res))) return rc;
+        if ((rc = launch(s, src, lo_end, hi_beg, res, 0))) return rc;
         if (!overlap) CU_TRY(cudaEventRecord(s.ev_boundary, s.compute));
     }
     if (c->snap_buf == dst) c->snap_buf = -1;
     if (c->slabs.size() > 1 || c->multi_process) {
-        int rc = exchange_ghosts(c, dst);
+        int rc = exchange_ghosts(c, dst, counted);
         if (rc) return rc;
     }
     c->cur = dst;
@@ -616,6 +656,7 @@ void destroy_slab(Slab& s)
     for (int b = 0; b < 2; ++b)
         if (s.buf[b]) cudaFree(s.buf[b]);
     if (s.d_res) cudaFree(s.d_res);
+    if (s.d_done) cudaFree(s.d_done);
     if (s.d_partial) cudaFree(s.d_partial);
     if (s.d_scalar) cudaFree(s.d_scalar);
     if (s.h_scalar) cudaFreeHost(s.h_scalar);
@@ -670,6 +711,8 @@ int setup_slab(heat3d_ctx* c, Slab& s)
         }
     }
     CU_TRY(cudaMalloc(&s.d_res, sizeof(unsigned long long)));
+    CU_TRY(cudaMalloc(&s.d_done, sizeof(unsigned long long)));
+    CU_TRY(cudaMemset(s.d_done, 0, sizeof(unsigned long long)));
     CU_TRY(cudaMemset(s.d_res, 0, sizeof(unsigned long long)));
     s.partial_blocks = s.num_sms * 8;
     CU_TRY(cudaMalloc(&s.d_partial, (size_t)s.partial_blocks * sizeof(double)));
@@ -898,6 +941,11 @@ int heat3d_create(const heat3d_params* pin, heat3d_ctx** out)
             if (!c->variant2) { delete c; return fail(HEAT3D_ERR_INVALID, "no depth-2 kernel variant matches HEAT3D_T2_TUNE=%s", e); }
             if (t[5] > 0) c->t2_chunk = t[5];
         }
+    }
+
+    if (p.nslabs > 1 && c->use_tma) {
+        const char* e = getenv("HEAT3D_END_SIGNAL");
+        c->end_signal = !(e && atoi(e) == 0) && load_stream_memops() == HEAT3D_OK;
     }
 
     c->slabs.resize(p.nlocal);

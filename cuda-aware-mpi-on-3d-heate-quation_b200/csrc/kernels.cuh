@@ -211,11 +211,38 @@ struct TmaCfg {
     static constexpr int SMEM_BYTES = STAGES * STAGE_STRIDE + 2 * STAGES * 8;
 };
 
+// How one launch covers its output planes.  "End" chunks are the ones whose results neighbouring slabs are waiting
+// for: they take the lowest block indices (so they are dispatched first) and every end-chunk CTA bumps `done` when
+// its planes are in memory; the exchange stream waits on that counter (a stream memory operation, no extra launch),
+// so ghost planes leave while the same kernel is still working on the middle of the slab.
 struct TmaWork {
-    int ntx, nty;          // tiles in x, y
-    int nchunks;           // z-chunks
-    int chunk_len;         // output planes per chunk (last one may be shorter)
+    int ntx, nty;                 // tiles in x, y
+    int n_end;                    // 0..2 end chunks, taken by CTAs [0, n_end * ntiles)
+    int end_za[2], end_zb[2];     // their output plane ranges
+    int mid_za, mid_zb;           // the rest, cut into chunks of chunk_len
+    int chunk_len;
+    unsigned long long* done;     // nullptr when nobody listens
 };
+
+__device__ __forceinline__ bool chunk_of_cta(const TmaWork& w, int cidx, int& zs, int& cnt)
+{
+    const bool is_end = cidx < w.n_end;
+    if (is_end) {
+        zs = w.end_za[cidx];
+        cnt = w.end_zb[cidx] - zs;
+    } else {
+        zs = w.mid_za + (cidx - w.n_end) * w.chunk_len;
+        cnt = min(w.chunk_len, w.mid_zb - zs);
+    }
+    return is_end;
+}
+
+__device__ __forceinline__ void signal_end_chunk(const TmaWork& w)
+{
+    __threadfence();              // this thread's stores are visible device-wide ...
+    __syncthreads();              // ... for every thread of the CTA ...
+    if (threadIdx.x == 0) atomicAdd(w.done, 1ULL);   // ... before the CTA is counted
+}
 
 // Per-thread store plan, fixed for the whole chunk: which of the thread's cells exist and are interior.
 struct StorePlan {
@@ -289,9 +316,8 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
     const int tid = threadIdx.x;
     const int ntiles = w.ntx * w.nty;
     const int tile = blockIdx.x % ntiles;
-    const int chunk = blockIdx.x / ntiles;
-    const int zs = g.za + chunk * w.chunk_len;                  // first output plane of this CTA
-    const int cnt = min(w.chunk_len, g.zb - zs);                // output planes of this CTA
+    int zs, cnt;                                                // first output plane / number of output planes of this CTA
+    const bool is_end = chunk_of_cta(w, blockIdx.x / ntiles, zs, cnt);
     if (cnt <= 0) return;
     const int niter = cnt + 2;                                  // input planes zs-1 .. zs+cnt
     const int bx = (tile % w.ntx) * TX - 2;                     // TMA box origin
@@ -416,6 +442,7 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
         }
     }
     if (RES) warp_residual_commit(rmax, res_slot);
+    if (is_end && w.done) signal_end_chunk(w);
 }
 
 // ------------------------------------------------------------------------------------------------------

@@ -107,9 +107,8 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     const int tid = threadIdx.x;
     const int ntiles = w.ntx * w.nty;
     const int tile = blockIdx.x % ntiles;
-    const int chunk = blockIdx.x / ntiles;
-    const int zs = g.za + chunk * w.chunk_len;                  // first output (time n+2) plane of this CTA
-    const int cnt = min(w.chunk_len, g.zb - zs);
+    int zs, cnt;                                                // first output (time n+2) plane / number of output planes
+    const bool is_end = chunk_of_cta(w, blockIdx.x / ntiles, zs, cnt);
     if (cnt <= 0) return;
     const int niter = cnt + 4;                                  // input planes zs-2 .. zs+cnt+1
     const int ox = (tile % w.ntx) * Cfg::OX, oy = (tile / w.ntx) * Cfg::OY;   // output tile origin
@@ -246,6 +245,7 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
         if (q + 1 < niter) body(q + 1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
     }
     if (RES) warp_residual_commit(rmax, res_slot);
+    if (is_end && w.done) signal_end_chunk(w);
 }
 
 }  // namespace h3

@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--kernel", default="auto", choices=["auto", "tma", "baseline"])
     ap.add_argument("--temporal-k", type=int, default=2, choices=[1, 2],
                     help="FTCS updates fused per HBM pass (2 = temporal blocking, bit-identical results)")
+    ap.add_argument("--grid", default="", help="nx,ny,nz: explicit global grid (experiments; overrides --workload)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -57,6 +58,9 @@ def workload(args, n):
         shape, name, scaling, ts = (1024, 1024, 512 * n), f"weak scaling 1024x1024x512-per-GPU fp64, z-slabs ({1024}x{1024}x{512 * n})", "weak", 250
     else:
         shape, name, scaling, ts = (1024, 1024, 1024), "1024^3 fp64 strong scaling, z-slab decomposition", "strong", 125 * n
+    if args.grid:
+        shape = tuple(int(v) for v in args.grid.split(","))
+        name, scaling = "custom grid %dx%dx%d" % shape, "strong"
     if args.tsteps:
         ts = args.tsteps
     return shape, name, scaling, ts

@@ -12,6 +12,7 @@
 //   HEAT3D_ARITH=strict|fma   arithmetic order of the update (default strict = the host program's)
 //   HEAT3D_CHECK_EVERY=N   examine the residual every N iterations (default 1 = reference semantics)
 //   HEAT3D_OUT_EVERY=M     also write output/out_<iteration>.dat every M iterations (async snapshots)
+//   HEAT3D_TEMPORAL_K=1|2  updates fused per HBM pass (bit-identical results; 2 pays off once CHECK_EVERY >= 2)
 //   HEAT3D_KERNEL=auto|tma|baseline
 //   HEAT3D_PERF=1          print GLUPS / algorithmic GB/s to stderr
 #include "../../include/heat3d.h"
@@ -141,6 +142,7 @@ int main(int argc, char** argv)
     p.arith = (arithEnv && std::string(arithEnv) == "fma") ? HEAT3D_ARITH_FMA : HEAT3D_ARITH_STRICT;
     if (kernEnv && std::string(kernEnv) == "baseline") p.kernel = HEAT3D_KERNEL_BASELINE;
     if (kernEnv && std::string(kernEnv) == "tma") p.kernel = HEAT3D_KERNEL_TMA;
+    p.temporal_k = (int32_t)std::max(1u, env_unsigned("HEAT3D_TEMPORAL_K", 1));
     std::vector<int32_t> devices(ndev);
     for (unsigned i = 0; i < ndev; ++i) devices[i] = (int32_t)i;
     p.nslabs = (int32_t)ndev; p.slab_first = 0; p.nlocal = (int32_t)ndev;

@@ -56,3 +56,30 @@ def test_driver_periodic_dumps_and_perf_line(h3, manifest, tmp_path):
     assert files == ["out.dat", "out_100.dat", "out_200.dat"]
     assert hashlib.md5(open(tmp_path / "output" / "out.dat", "rb").read()).hexdigest() == m["dump_md5"]
     assert os.path.getsize(tmp_path / "output" / "out_100.dat") == m["dump_bytes"]
+
+
+def test_driver_temporal_blocking_same_output(h3, manifest, tmp_path):
+    """HEAT3D_TEMPORAL_K=2 + residual checked every 4th iteration: different kernels, byte-identical dump."""
+    m = manifest["aniso_33x17x65"]
+    r = _run(h3, m["args"], str(tmp_path), {"HEAT3D_TEMPORAL_K": "2", "HEAT3D_CHECK_EVERY": "4"})
+    assert r.returncode == 0, r.stderr
+    assert _report(r.stdout) == m["stdout"]
+    assert hashlib.md5(open(tmp_path / "output" / "out.dat", "rb").read()).hexdigest() == m["dump_md5"]
+
+
+@pytest.mark.parametrize("ndev", [2, 4])
+@pytest.mark.parametrize("k", [1, 2])
+def test_driver_multi_gpu_in_one_process(h3, manifest, tmp_path, ndev, k):
+    """HEAT3D_NDEV=P: one process drives P GPUs (peer copies between slabs) - the reference's `mpirun -n P`;
+    the dump is the single-zone form and must equal the single-domain result byte for byte."""
+    import torch
+    if torch.cuda.device_count() < ndev:
+        pytest.skip(f"needs {ndev} GPUs")
+    for name in ("c27_converge", "c64_1000"):
+        m = manifest[name]
+        wd = tmp_path / f"{name}_{ndev}_{k}"
+        wd.mkdir()
+        r = _run(h3, m["args"], str(wd), {"HEAT3D_NDEV": str(ndev), "HEAT3D_TEMPORAL_K": str(k)})
+        assert r.returncode == 0, r.stderr
+        assert _report(r.stdout) == m["stdout"]
+        assert hashlib.md5(open(wd / "output" / "out.dat", "rb").read()).hexdigest() == m["dump_md5"]

@@ -207,3 +207,21 @@ def test_large_grid_properties(h3):
     assert np.max(np.abs(T - T[::-1, :, :])) < 1e-13
     assert np.max(np.abs(T - T[:, :, ::-1])) < 1e-13
     assert t["steps"] == 100 and t["launches"] >= 100
+
+
+@pytest.mark.parametrize("k", [1, 2])
+def test_multi_device_one_process_bitwise(h3, oracle, k):
+    """Slabs on distinct GPUs driven by one context (cudaMemcpyPeerAsync between devices)."""
+    import torch
+    nd = min(torch.cuda.device_count(), 4)
+    if nd < 2:
+        pytest.skip("needs >= 2 GPUs")
+    nx, ny, nz, nsteps = 150, 70, 46, 15
+    ref = _oracle_field(oracle, nx, ny, nz, nsteps)
+    with h3.Heat3D(nx, ny, nz, temporal_k=k, nslabs=nd, devices=list(range(nd))) as sim:
+        assert sim.exchange_name() == "peer-copy"
+        sim.init_reference_field()
+        res = sim.step_residual(nsteps)
+        got = sim.download()
+    assert np.array_equal(got, ref)
+    assert res == oracle.residual(ref, _oracle_field(oracle, nx, ny, nz, nsteps - 1))

@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--temporal-k", type=int, default=2, choices=[1, 2],
                     help="FTCS updates fused per HBM pass (2 = temporal blocking, bit-identical results)")
     ap.add_argument("--grid", default="", help="nx,ny,nz: explicit global grid (experiments; overrides --workload)")
+    ap.add_argument("--snapshot-every", type=int, default=0,
+                    help="async snapshot of the field to pinned host memory every M bench steps inside the timed loop")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -214,14 +216,20 @@ def main():
     if rank == 0:
         sampler.start()
     dev_ms, launches, stencil_launches, halo_ms = 0.0, 0, 0, 0.0
+    snap_buf, nsnap = (h3.pinned_empty((z1 - z0, ny, nx)), 0) if args.snapshot_every else (None, 0)
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for it in range(args.steps):
+        if snap_buf is not None and it % args.snapshot_every == 0:
+            sim.snapshot_async_local(snap_buf)      # D2H on the copy stream while the next updates run
+            nsnap += 1
         sim.step(tsteps)
         tm = sim.timing()                     # waits for this step's events; device time of the call
         dev_ms += tm["last_call_ms"]
         launches += tm["last_call_launches"]
         stencil_launches += tm["last_call_stencil_launches"]
         halo_ms += tm["exposed_halo_ms"]
+    if snap_buf is not None:
+        sim.snapshot_wait()
     barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop() if rank == 0 else None
@@ -293,7 +301,8 @@ def main():
                            "decomposition": f"{n} z-slab(s), one process per GPU" + (", ghost planes by NCCL send/recv overlapped with interior compute" if n > 1 else ""),
                            "l2": "inputs exceed L2 (two %.1f GiB buffers per GPU vs 126 MB)" % ((z1 - z0) * ny * nx * 8 / 2**30)},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-                "wall_ms_per_step": wall_ms / args.steps, "exposed_halo_ms_per_update": halo_ms / (tsteps * args.steps) if n > 1 else None,
+                "wall_ms_per_step": wall_ms / args.steps, "snapshots": {"count": nsnap, "bytes_each_per_rank": int(snap_buf.nbytes)} if snap_buf is not None else None,
+                "wall_glups_incl_snapshots": total_updates / (wall_ms * 1e-3) / 1e9, "exposed_halo_ms_per_update": halo_ms / (tsteps * args.steps) if n > 1 else None,
                 "roofline_glups_at_peak": peak / (16.0 / k)}
         print(json.dumps(line), flush=True)
     sim.close()

@@ -174,29 +174,29 @@ const std::vector<TmaVariant>& variants()
 // ---- depth-2 temporal-blocking kernel variants --------------------------------------------------------
 struct T2Variant {
     const char* name;
-    int cx, cy, ry, stages, minb;
+    int cx, cy, ry, stages, minb, sched;
     size_t smem;
     int threads;
     const void* fn[2][2];   // [arith][res]
 };
 
-template <int CX, int CY, int RY, int ST, int MINB>
+template <int CX, int CY, int RY, int ST, int MINB, int SCHED = 0>
 T2Variant make_t2(const char* name)
 {
     T2Variant v;
     v.name = name;
-    v.cx = CX; v.cy = CY; v.ry = RY; v.stages = ST; v.minb = MINB;
+    v.cx = CX; v.cy = CY; v.ry = RY; v.stages = ST; v.minb = MINB; v.sched = SCHED;
     v.smem = h3::Tma2Cfg<CX, CY, ST>::SMEM_BYTES;
     v.threads = (CX / 2) * (CY / RY);
-    v.fn[0][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, false, MINB>;
-    v.fn[0][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, true, MINB>;
-    v.fn[1][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, false, MINB>;
-    v.fn[1][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, true, MINB>;
+    v.fn[0][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, false, MINB, SCHED>;
+    v.fn[0][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, true, MINB, SCHED>;
+    v.fn[1][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, false, MINB, SCHED>;
+    v.fn[1][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, true, MINB, SCHED>;
     return v;
 }
 
 // compute region cx x cy (output tile (cx-4) x (cy-2)), rows/thread, stages, CTAs/SM.  First = default;
-// HEAT3D_T2_TUNE="cx,cy,ry,stages,ctas[,chunk_len]" selects another (experiments).
+// HEAT3D_T2_TUNE="cx,cy,ry,stages,ctas[,chunk_len[,sched]]" selects another (experiments).
 const std::vector<T2Variant>& t2_variants()
 {
     static const std::vector<T2Variant> v = {
@@ -207,6 +207,11 @@ const std::vector<T2Variant>& t2_variants()
         make_t2<128, 16, 2, 4, 1>("t2_128x16_r2_s4_c1"),
         make_t2<128, 16, 2, 3, 1>("t2_128x16_r2_s3_c1"),
         make_t2<128, 8, 2, 4, 2>("t2_128x8_r2_s4_c2"),
+        // "_L" = schedule 1 (only centre values live across iterations: 80 registers, 3 CTAs/SM).  Measured no faster
+        // than schedule 0 (profiles/r01_sweep_k2_sched1.txt): the kernel is bound by shared-memory wavefronts and FP64
+        // issue, not by latency that more resident warps could hide.
+        make_t2<64, 16, 2, 4, 3, 1>("t2_64x16_r2_s4_c3_L"),
+        make_t2<64, 16, 2, 3, 3, 1>("t2_64x16_r2_s3_c3_L"),
     };
     return v;
 }
@@ -933,11 +938,11 @@ int heat3d_create(const heat3d_params* pin, heat3d_ctx** out)
         const auto& vs = t2_variants();
         c->variant2 = &vs[0];
         if (const char* e = getenv("HEAT3D_T2_TUNE")) {
-            int t[6] = {0, 0, 0, 0, 0, 0};
-            sscanf(e, "%d,%d,%d,%d,%d,%d", &t[0], &t[1], &t[2], &t[3], &t[4], &t[5]);
+            int t[7] = {0, 0, 0, 0, 0, 0, 0};
+            sscanf(e, "%d,%d,%d,%d,%d,%d,%d", &t[0], &t[1], &t[2], &t[3], &t[4], &t[5], &t[6]);
             c->variant2 = nullptr;
             for (const T2Variant& v : vs)
-                if (t[0] == v.cx && t[1] == v.cy && t[2] == v.ry && t[3] == v.stages && t[4] == v.minb) { c->variant2 = &v; break; }
+                if (t[0] == v.cx && t[1] == v.cy && t[2] == v.ry && t[3] == v.stages && t[4] == v.minb && t[6] == v.sched) { c->variant2 = &v; break; }
             if (!c->variant2) { delete c; return fail(HEAT3D_ERR_INVALID, "no depth-2 kernel variant matches HEAT3D_T2_TUNE=%s", e); }
             if (t[5] > 0) c->t2_chunk = t[5];
         }

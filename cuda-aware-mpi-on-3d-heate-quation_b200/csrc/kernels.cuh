@@ -227,9 +227,9 @@ struct TmaWork {
 __device__ __forceinline__ bool chunk_of_cta(const TmaWork& w, int cidx, int& zs, int& cnt)
 {
     const bool is_end = cidx < w.n_end;
-    if (is_end) {
-        zs = w.end_za[cidx];
-        cnt = w.end_zb[cidx] - zs;
+    if (is_end) {      // (selects, not indexing: a dynamically indexed kernel parameter would be copied to local memory)
+        zs = cidx == 0 ? w.end_za[0] : w.end_za[1];
+        cnt = (cidx == 0 ? w.end_zb[0] : w.end_zb[1]) - zs;
     } else {
         zs = w.mid_za + (cidx - w.n_end) * w.chunk_len;
         cnt = min(w.chunk_len, w.mid_zb - zs);

@@ -60,6 +60,24 @@ __device__ __forceinline__ void level_step(const double2 (&cn)[RY], const double
     }
 }
 
+// whole update of one plane in one go (same operations, same order as partial_xy2 followed by finish_z2)
+template <int RY, int ARITH>
+__device__ __forceinline__ void level_full(const double2 (&c)[RY], const double (&xl)[RY], const double (&xr)[RY], const double2& up,
+                                           const double2& dn, const double2 (&zm)[RY], const double2 (&zp)[RY], double2 (&o)[RY],
+                                           double Dx, double Dy, double Dz)
+{
+#pragma unroll
+    for (int r = 0; r < RY; ++r) {
+        const double2 ym = r == 0 ? up : c[r - 1];
+        const double2 yp = r == RY - 1 ? dn : c[r + 1];
+        const double twx = twice(c[r].x), twy = twice(c[r].y);
+        const double tx = partial_xy2<ARITH>(c[r].x, twx, xl[r], c[r].y, ym.x, yp.x, Dx, Dy);
+        const double ty = partial_xy2<ARITH>(c[r].y, twy, c[r].x, xr[r], ym.y, yp.y, Dx, Dy);
+        o[r].x = finish_z2<ARITH>(tx, twx, zm[r].x, zp[r].x, Dz);
+        o[r].y = finish_z2<ARITH>(ty, twy, zm[r].y, zp[r].y, Dz);
+    }
+}
+
 // xy neighbours of a thread's 2 x RY patch, read from the staged plane.  SHFL = take the x neighbours from the
 // adjacent lanes' registers by warp shuffle instead (edge lanes still read the halo column): the kernel is bound
 // by shared-memory wavefronts (ncu: l1tex 80 %), and a strided 8-byte load costs 4 wavefronts per warp, but the four
@@ -84,7 +102,11 @@ __device__ __forceinline__ void load_neighbours(const double* __restrict__ S, in
     }
 }
 
-template <int CX, int CY, int RY, int STAGES, int ARITH, bool RES, int MINB>
+// SCHED 0: each level keeps partial_xy of its newest plane in registers and finishes it when the next plane shows up.
+// SCHED 1: nothing but centre values lives across iterations: a staged plane stays resident one iteration longer and
+//          the whole update of plane p-1 is formed when plane p has arrived (level 1), likewise for level 2 from the
+//          previous mid plane.  Same arithmetic, ~32 fewer registers per thread.
+template <int CX, int CY, int RY, int STAGES, int ARITH, bool RES, int MINB, int SCHED>
 __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     stencil_tma_t2_kernel(const __grid_constant__ CUtensorMap tmap, double* __restrict__ dst, Geom g, TmaWork w, int z1lo, int z1hi,
                           unsigned long long* res_slot)
@@ -98,7 +120,7 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
 #else
     constexpr bool SHFL_X = false;
 #endif
-    static_assert(CX % 64 == 0 && CY % RY == 0 && NTHR % 32 == 0 && NTHR <= 1024 && STAGES >= 2, "tile shape");
+    static_assert(CX % 64 == 0 && CY % RY == 0 && NTHR % 32 == 0 && NTHR <= 1024 && STAGES >= 2 + SCHED, "tile shape");
 
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* mid = smem + STAGES * Cfg::STAGE_STRIDE;
@@ -230,20 +252,87 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
         par ^= 1;
     };
 
+    // SCHED 1 body.  Input plane q sits in stage q % STAGES, plane q-1 is still in the previous stage.
+    auto body1 = [&](int q, double2 (&c0n)[RY], const double2 (&c0p1)[RY], const double2 (&c0p2)[RY], double2 (&c1n)[RY],
+                     const double2 (&c1p1)[RY], const double2 (&c1p2)[RY]) {
+        const uint32_t sprev = s == 0 ? STAGES - 1 : s - 1;
+        const double* S = (const double*)(smem + s * Cfg::STAGE_STRIDE) + soff;
+        const double* Sp = (const double*)(smem + sprev * Cfg::STAGE_STRIDE) + soff;
+        mbar_wait(&full[s], ph);
+#pragma unroll
+        for (int r = 0; r < RY; ++r) c0n[r] = *(const double2*)(S + r * ROW);
+        double xl[RY], xr[RY];
+        double2 up, dn;
+        if (q >= 2) {   // level 1: plane q-1 of the run = local plane zs + q - 3
+            load_neighbours<RY, false>(Sp, ROW, c0p1, lane, xl, xr, up, dn);
+            level_full<RY, ARITH>(c0p1, xl, xr, up, dn, c0p2, c0n, c1n, g.Dx, g.Dy, g.Dz);
+            const int z1 = zs + q - 3;
+            const bool zint = z1 >= z1lo && z1 < z1hi;
+            if (!(zint && pl.all1)) {           // Dirichlet cells / planes keep their value
+#pragma unroll
+                for (int r = 0; r < RY; ++r) {
+                    const bool row = zint && ((pl.rows1 >> r) & 1u);
+                    if (!(row && pl.i1x0)) c1n[r].x = c0p1[r].x;
+                    if (!(row && pl.i1x1)) c1n[r].y = c0p1[r].y;
+                }
+            }
+            double* M = (double*)(mid + par * Cfg::STAGE_STRIDE) + soff;
+#pragma unroll
+            for (int r = 0; r < RY; ++r) *(double2*)(M + r * ROW) = c1n[r];
+        }
+        if (q >= 4) {   // level 2: local plane zs + q - 4, from the mid plane published one iteration ago
+            const double* Mp = (const double*)(mid + (par ^ 1) * Cfg::STAGE_STRIDE) + soff;
+            load_neighbours<RY, false>(Mp, ROW, c1p1, lane, xl, xr, up, dn);
+            double2 o[RY];
+            level_full<RY, ARITH>(c1p1, xl, xr, up, dn, c1p2, c1n, o, g.Dx, g.Dy, g.Dz);
+#pragma unroll
+            for (int r = 0; r < RY; ++r) {
+                double* o_ptr = out + (long long)r * g.pitch;
+                if (pl.st.all) {
+                    *(double2*)o_ptr = o[r];
+                    if (RES) rmax = fmax(rmax, fmax(fabs(__dsub_rn(o[r].x, c1p1[r].x)), fabs(__dsub_rn(o[r].y, c1p1[r].y))));
+                } else if ((pl.st.rows >> r) & 1u) {
+                    if (pl.st.x0) {
+                        o_ptr[0] = o[r].x;
+                        if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o[r].x, c1p1[r].x)));
+                    }
+                    if (pl.st.x1) {
+                        o_ptr[1] = o[r].y;
+                        if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o[r].y, c1p1[r].y)));
+                    }
+                }
+            }
+            out += g.plane;
+        }
+        __syncthreads();        // plane q-1's stage has been read by everyone; this iteration's mid plane is complete
+        if (q >= 1 && warp == (q & (NWARP - 1)) && lane == 0 && q - 1 + STAGES < niter) {
+            mbar_arrive_expect_tx(&full[sprev], Cfg::STAGE_BYTES);
+            tma_load_3d(smem + sprev * Cfg::STAGE_STRIDE, &tmap, &full[sprev], bx, by, zs - 2 + q - 1 + STAGES);
+        }
+        if (++s == STAGES) { s = 0; ph ^= 1u; }
+        par ^= 1;
+    };
+
     // Register rotation: level 0 newest = C0[q % 3]; level 1 newest (plane q-1 of the run) = C1[(q + 2) % 3].
-    body(0, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
-    body(1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
-    body(2, C0[2], C0[1], C0[0], C1[1], C1[0], C1[2]);
+#define H3_T2_BODY(qq, a, b, c, d, e, f)                                  \
+    do {                                                                  \
+        if (SCHED == 1) body1(qq, a, b, c, d, e, f);                      \
+        else body(qq, a, b, c, d, e, f);                                  \
+    } while (0)
+    H3_T2_BODY(0, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
+    H3_T2_BODY(1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
+    H3_T2_BODY(2, C0[2], C0[1], C0[0], C1[1], C1[0], C1[2]);
     int q = 3;
     for (; q + 2 < niter; q += 3) {
-        body(q, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
-        body(q + 1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
-        body(q + 2, C0[2], C0[1], C0[0], C1[1], C1[0], C1[2]);
+        H3_T2_BODY(q, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
+        H3_T2_BODY(q + 1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
+        H3_T2_BODY(q + 2, C0[2], C0[1], C0[0], C1[1], C1[0], C1[2]);
     }
     if (q < niter) {
-        body(q, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
-        if (q + 1 < niter) body(q + 1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
+        H3_T2_BODY(q, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
+        if (q + 1 < niter) H3_T2_BODY(q + 1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
     }
+#undef H3_T2_BODY
     if (RES) warp_residual_commit(rmax, res_slot);
     if (is_end && w.done) signal_end_chunk(w);
 }

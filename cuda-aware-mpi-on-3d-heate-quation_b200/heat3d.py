@@ -253,6 +253,14 @@ class Heat3D:
     def snapshot_async(self, pinned):
         _check(lib().heat3d_snapshot_async(self._ctx, self._arr(pinned)))
 
+    def snapshot_async_local(self, pinned_local):
+        """As snapshot_async, for a pinned array that holds only THIS context's planes (shape (z1-z0, ny, nx)): the C
+        entry point addresses planes by their global index, so it is handed the address plane 0 would have."""
+        z0, z1 = self.local_range()
+        assert pinned_local.dtype == np.float64 and pinned_local.flags["C_CONTIGUOUS"] and pinned_local.shape == (z1 - z0, self.ny, self.nx)
+        base = pinned_local.ctypes.data - z0 * self.ny * self.nx * 8
+        _check(lib().heat3d_snapshot_async(self._ctx, C.cast(C.c_void_p(base), _dp)))
+
     def snapshot_wait(self):
         _check(lib().heat3d_snapshot_wait(self._ctx))
 

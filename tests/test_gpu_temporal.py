@@ -9,7 +9,9 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-T2_TUNES = ["64,32,2,4,1", "64,32,2,3,1", "64,16,2,4,2", "64,16,2,3,2", "128,16,2,4,1", "128,16,2,3,1", "128,8,2,4,2"]
+# cx,cy,rows/thread,stages,CTAs/SM[,chunk_len,schedule]
+T2_TUNES = ["64,32,2,4,1", "64,32,2,3,1", "64,16,2,4,2", "64,16,2,3,2", "128,16,2,4,1", "128,16,2,3,1", "128,8,2,4,2",
+            "64,16,2,4,3,7,1", "64,16,2,3,3,7,1"]
 
 
 @pytest.fixture(scope="module")
@@ -48,11 +50,12 @@ def test_depth2_bit_exact_vs_oracle(h3, oracle, shape, nsteps):
 @pytest.mark.parametrize("tune", T2_TUNES)
 def test_every_depth2_variant(h3, oracle, tune):
     nx, ny, nz, nsteps = 150, 70, 41, 10
-    os.environ["HEAT3D_T2_TUNE"] = tune + ",7"        # short chunks: several chunk seams inside the grid
+    f = tune.split(",")
+    os.environ["HEAT3D_T2_TUNE"] = tune if len(f) > 5 else tune + ",7"        # short chunks: several chunk seams inside the grid
     ref = _oracle_field(oracle, nx, ny, nz, nsteps)
     prev = _oracle_field(oracle, nx, ny, nz, nsteps - 1)
     with h3.Heat3D(nx, ny, nz, temporal_k=2) as sim:
-        assert sim.kernel_name() == "t2_%sx%s_r%s_s%s_c%s" % tuple(tune.split(","))
+        assert sim.kernel_name() == "t2_%sx%s_r%s_s%s_c%s" % tuple(f[:5]) + ("_L" if len(f) > 6 and f[6] == "1" else "")
         sim.init_reference_field()
         res = sim.step_residual(nsteps)               # even count: the residual comes out of the depth-2 kernel
         got = sim.download()

@@ -23,7 +23,8 @@ cells = (n - 2) ** 3
 for arith in (0, 1):
     for tune in TUNES:
         for ch in CHUNKS:
-            os.environ["HEAT3D_T2_TUNE"] = f"{tune},{ch}"
+            base, sched = (tune[:-1], 1) if tune.endswith("L") else (tune, 0)
+            os.environ["HEAT3D_T2_TUNE"] = f"{base},{ch},{sched}"
             try:
                 with h3.Heat3D(n, n, n, arith=arith, temporal_k=2) as sim:
                     sim.init_reference_field()

@@ -246,6 +246,7 @@ struct Slab {
     double* peer_buf[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
     unsigned long long* peer_flags[2] = {nullptr, nullptr};
     unsigned long long* d_flags = nullptr;
+    double* snap_dev = nullptr;              // device-side staging copy of the owned planes for async snapshots (lazily allocated)
     unsigned long long* d_done = nullptr;    // end-chunk CTAs finished so far (device counter the exchange stream waits on)
     unsigned long long done_target = 0;      // value d_done reaches when every end chunk launched so far is in memory
     bool lower = false, upper = false;     // has a neighbouring slab below / above
@@ -662,6 +663,7 @@ void destroy_slab(Slab& s)
         if (s.buf[b]) cudaFree(s.buf[b]);
     if (s.d_res) cudaFree(s.d_res);
     if (s.d_done) cudaFree(s.d_done);
+    if (s.snap_dev) cudaFree(s.snap_dev);
     if (s.d_partial) cudaFree(s.d_partial);
     if (s.d_scalar) cudaFree(s.d_scalar);
     if (s.h_scalar) cudaFreeHost(s.h_scalar);
@@ -1270,16 +1272,34 @@ int heat3d_snapshot_async(heat3d_ctx* c, double* pinned)
     int rc = check_ctx(c);
     if (rc) return rc;
     if (!pinned) return fail(HEAT3D_ERR_INVALID, "null host pointer");
-    if (c->snap_buf >= 0 && (rc = heat3d_snapshot_wait(c))) return rc;
+    if ((rc = heat3d_snapshot_wait(c))) return rc;           // one snapshot in flight at a time
     const size_t plane_host = (size_t)c->p.nx * c->p.ny;
+    bool staged = true;
     for (Slab& s : c->slabs) {
         if ((rc = set_dev(s))) return rc;
-        CU_TRY(cudaEventRecord(s.ev_tmp, s.compute));
-        CU_TRY(cudaStreamWaitEvent(s.copy, s.ev_tmp, 0));
-        if ((rc = copy_planes(s, c->cur, c->p.nx, c->p.ny, s.G, s.z1 - s.z0, pinned + (size_t)s.z0 * plane_host, false, s.copy))) return rc;
+        const uint32_t nzl = s.z1 - s.z0;
+        const size_t bytes = (size_t)nzl * s.plane * sizeof(double);
+        if (!s.snap_dev && cudaMalloc(&s.snap_dev, bytes) != cudaSuccess) { cudaGetLastError(); s.snap_dev = nullptr; }
+        if (s.snap_dev) {
+            // a device-to-device copy at HBM speed freezes the time level on the compute stream (milliseconds); the slow
+            // trip over PCIe then reads the frozen copy on the copy stream and never holds a field buffer hostage
+            CU_TRY(cudaMemcpyAsync(s.snap_dev, s.buf[c->cur] + (long long)s.G * s.plane, bytes, cudaMemcpyDeviceToDevice, s.compute));
+            CU_TRY(cudaEventRecord(s.ev_tmp, s.compute));
+            CU_TRY(cudaStreamWaitEvent(s.copy, s.ev_tmp, 0));
+            double* host = pinned + (size_t)s.z0 * plane_host;
+            const size_t rows = (size_t)c->p.ny * nzl, row_bytes = (size_t)c->p.nx * 8;
+            if (s.pitch == c->p.nx) CU_TRY(cudaMemcpyAsync(host, s.snap_dev, rows * row_bytes, cudaMemcpyDeviceToHost, s.copy));
+            else CU_TRY(cudaMemcpy2DAsync(host, row_bytes, s.snap_dev, (size_t)s.pitch * 8, row_bytes, rows, cudaMemcpyDeviceToHost, s.copy));
+        } else {
+            // no room for a staging copy: read the field buffer itself; the step that would overwrite it waits on the device
+            staged = false;
+            CU_TRY(cudaEventRecord(s.ev_tmp, s.compute));
+            CU_TRY(cudaStreamWaitEvent(s.copy, s.ev_tmp, 0));
+            if ((rc = copy_planes(s, c->cur, c->p.nx, c->p.ny, s.G, nzl, pinned + (size_t)s.z0 * plane_host, false, s.copy))) return rc;
+        }
         CU_TRY(cudaEventRecord(s.ev_snap, s.copy));
     }
-    c->snap_buf = c->cur;
+    c->snap_buf = staged ? -1 : c->cur;
     return HEAT3D_OK;
 }
 

@@ -173,10 +173,13 @@ int heat3d_mean_abs_error_vs_y_noalloc(const double* d_field, uint32_t nx, uint3
 
 /* ---- snapshots, sync, diagnostics --------------------------------------------------------------------- */
 
-/* Asynchronous copy of the current time level into PINNED host memory (global layout; own planes only) on a
- * copy stream, overlapping further heat3d_step calls; stepping that would overwrite the level being copied
- * waits on the device, not the host.  Replaces the blocking gather cu:1114-1124.  heat3d_snapshot_wait
- * blocks until the copy has landed. */
+/* Asynchronous copy of the current time level into PINNED host memory (global layout; own planes only), overlapping
+ * further heat3d_step calls: the level is first frozen by a device-to-device copy into a staging buffer (allocated
+ * on first use, one slab's worth of planes per GPU; milliseconds at HBM speed, ordered on the compute stream), then
+ * travels over PCIe on a copy stream while stepping continues.  If the staging buffer cannot be allocated the field
+ * buffer itself is read and the step that would overwrite it waits on the device, not the host.  One snapshot is
+ * in flight at a time (a second call waits for the first).  Replaces the blocking gather cu:1114-1124.
+ * heat3d_snapshot_wait blocks until the copy has landed. */
 int heat3d_snapshot_async(heat3d_ctx* ctx, double* pinned_host_global);
 int heat3d_snapshot_wait(heat3d_ctx* ctx);
 

@@ -200,11 +200,11 @@ def main():
             dist.barrier()
         sim.sync()
 
-    def max_over_ranks(x):
+    def max_over_ranks(x, op=None):
         if world == 1:
             return x
         t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=op or dist.ReduceOp.MAX)
         return float(t.item())
 
     # ---------------- device-resident throughput ----------------
@@ -235,6 +235,7 @@ def main():
     clocks = sampler.stop() if rank == 0 else None
     dev_ms = max_over_ranks(dev_ms)
     wall_ms = max_over_ranks(wall_ms)
+    halo_ms_min = max_over_ranks(halo_ms, dist.ReduceOp.MIN) if world > 1 else halo_ms
     halo_ms = max_over_ranks(halo_ms)
     total_updates = cells * tsteps * args.steps
     value = total_updates / (dev_ms * 1e-3) / 1e9
@@ -303,6 +304,8 @@ def main():
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
                 "wall_ms_per_step": wall_ms / args.steps, "snapshots": {"count": nsnap, "bytes_each_per_rank": int(snap_buf.nbytes)} if snap_buf is not None else None,
                 "wall_glups_incl_snapshots": total_updates / (wall_ms * 1e-3) / 1e9, "exposed_halo_ms_per_update": halo_ms / (tsteps * args.steps) if n > 1 else None,
+                "exposed_halo_ms_per_update_min_rank": halo_ms_min / (tsteps * args.steps) if n > 1 else None,
+                "exchange": sim.exchange_name(),
                 "roofline_glups_at_peak": peak / (16.0 / k)}
         print(json.dumps(line), flush=True)
     sim.close()

@@ -9,6 +9,7 @@ import __graft_entry__ as ge  # noqa: E402
 
 h3 = ge.load_package()
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 512
+shape = tuple(int(v) for v in os.environ["SWEEP_SHAPE"].split(",")) if os.environ.get("SWEEP_SHAPE") else (n, n, n)
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 200
 sustained = os.environ.get("SWEEP_SUSTAINED") == "1"
 warm, reps = (steps, 2) if sustained else (20, 3)
@@ -19,14 +20,14 @@ except Exception:
     pass
 TUNES = [t for t in os.environ.get("SWEEP_TUNES", "64,32,2,4,1;64,32,2,3,1;64,16,2,4,2;64,16,2,3,2;128,16,2,4,1;128,16,2,3,1;128,8,2,4,2").split(";")]
 CHUNKS = [int(c) for c in os.environ.get("SWEEP_CHUNKS", "16,32,64").split(",")]
-cells = (n - 2) ** 3
-for arith in (0, 1):
+cells = (shape[0] - 2) * (shape[1] - 2) * (shape[2] - 2)
+for arith in ((0,) if os.environ.get("SWEEP_STRICT_ONLY") else (0, 1)):
     for tune in TUNES:
         for ch in CHUNKS:
             base, sched = (tune[:-1], 1) if tune.endswith("L") else (tune, 0)
             os.environ["HEAT3D_T2_TUNE"] = f"{base},{ch},{sched}"
             try:
-                with h3.Heat3D(n, n, n, arith=arith, temporal_k=2) as sim:
+                with h3.Heat3D(*shape, arith=arith, temporal_k=2) as sim:
                     sim.init_reference_field()
                     sim.step(warm)
                     sim.sync()

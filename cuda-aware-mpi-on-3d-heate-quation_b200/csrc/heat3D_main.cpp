@@ -165,6 +165,14 @@ int main(int argc, char** argv)
     unsigned applied = 0, nsnap = 0;
     const auto start = std::chrono::steady_clock::now();      // cu:527
     unsigned time = 0;
+    if (!outEvery) {
+        // the whole loop inside the library: same norm / break logic (cu:1030-1073), and with checkEvery == 1 the next
+        // iteration is already queued while the host looks at a residual, so the GPU never waits for the host
+        int32_t conv = 0;
+        H3(heat3d_run(ctx, iterMax, eps, checkEvery, &finalNumIterations, &conv, &applied));
+        globalBreakCondition = conv;
+        time = iterMax;
+    }
     while (time < iterMax) {
         // next iteration whose residual is examined: 0, then every checkEvery-th, and the last one
         unsigned target = time == 0 ? 0 : ((time / checkEvery) + 1) * checkEvery - 1;

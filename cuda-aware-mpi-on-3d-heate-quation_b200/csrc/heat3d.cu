@@ -233,7 +233,9 @@ struct Slab {
     cudaEvent_t ev_boundary = nullptr, ev_put = nullptr, ev_start = nullptr, ev_stop = nullptr, ev_snap = nullptr,
                 ev_tmp = nullptr;
     std::vector<cudaEvent_t> ev_wait0, ev_wait1;   // HEAT3D_FLAG_TIME_HALO: brackets of the ghost wait, ring of HALO_RING steps
-    unsigned long long* d_res = nullptr;   // residual slot (bit pattern of a non-negative double)
+    unsigned long long* d_res = nullptr;   // residual slot in use (bit pattern of a non-negative double); = d_res_base + 0 or 1
+    unsigned long long* d_res_base = nullptr;
+    cudaEvent_t ev_res[2] = {nullptr, nullptr};   // pipelined convergence loop: residual of slot i has reached the host
     double* d_partial = nullptr;           // error-norm scratch: partial sums
     double* d_scalar = nullptr;            // error-norm result / allreduce staging
     double* h_scalar = nullptr;            // pinned: 2 doubles
@@ -270,6 +272,7 @@ struct heat3d_ctx {
     double last_res = 0.0;
     heat3d_timing tm;
     bool halo_timed = false;
+    bool res_slot_prezeroed = false;   // pipelined convergence loop: residual slots are cleared off the compute stream
     bool end_signal = false;           // stream memory operations available: single-launch steps with end-chunk signalling
     unsigned long long seq = 0;        // number of ghost exchanges issued so far (same on every process)
     bool timing_pending = false;       // a call's ev_start/ev_stop have not been folded into tm yet
@@ -526,7 +529,7 @@ int step_block(heat3d_ctx* c, int k, bool res)
         int rc = set_dev(s);
         if (rc) return rc;
         if (c->snap_buf == dst) CU_TRY(cudaStreamWaitEvent(s.compute, s.ev_snap, 0));
-        if (res) CU_TRY(cudaMemsetAsync(s.d_res, 0, sizeof(unsigned long long), s.compute));
+        if (res && !c->res_slot_prezeroed) CU_TRY(cudaMemsetAsync(s.d_res, 0, sizeof(unsigned long long), s.compute));
         if (!s.lower && !s.upper) {
             if ((rc = launch(s, src, s.za, s.zb, res, 0))) return rc;
             continue;
@@ -661,7 +664,9 @@ void destroy_slab(Slab& s)
     if (s.nccl && g_nccl.CommDestroy) g_nccl.CommDestroy(s.nccl);
     for (int b = 0; b < 2; ++b)
         if (s.buf[b]) cudaFree(s.buf[b]);
-    if (s.d_res) cudaFree(s.d_res);
+    if (s.d_res_base) cudaFree(s.d_res_base);
+    for (cudaEvent_t e : s.ev_res)
+        if (e) cudaEventDestroy(e);
     if (s.d_done) cudaFree(s.d_done);
     if (s.snap_dev) cudaFree(s.snap_dev);
     if (s.d_partial) cudaFree(s.d_partial);
@@ -717,14 +722,16 @@ int setup_slab(heat3d_ctx* c, Slab& s)
             CU_TRY(cudaEventCreate(&s.ev_wait1[i]));
         }
     }
-    CU_TRY(cudaMalloc(&s.d_res, sizeof(unsigned long long)));
+    CU_TRY(cudaMalloc(&s.d_res_base, 2 * sizeof(unsigned long long)));
+    s.d_res = s.d_res_base;
+    for (cudaEvent_t& e : s.ev_res) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     CU_TRY(cudaMalloc(&s.d_done, sizeof(unsigned long long)));
     CU_TRY(cudaMemset(s.d_done, 0, sizeof(unsigned long long)));
-    CU_TRY(cudaMemset(s.d_res, 0, sizeof(unsigned long long)));
+    CU_TRY(cudaMemset(s.d_res_base, 0, 2 * sizeof(unsigned long long)));
     s.partial_blocks = s.num_sms * 8;
     CU_TRY(cudaMalloc(&s.d_partial, (size_t)s.partial_blocks * sizeof(double)));
     CU_TRY(cudaMalloc(&s.d_scalar, 2 * sizeof(double)));
-    CU_TRY(cudaHostAlloc(&s.h_scalar, 2 * sizeof(double), cudaHostAllocDefault));
+    CU_TRY(cudaHostAlloc(&s.h_scalar, 4 * sizeof(double), cudaHostAllocDefault));   // [0..1] queries, [2..3] pipelined residuals
     // local output range: owned planes that are global interior planes
     long long a = (long long)s.G, b = (long long)s.G + (s.z1 - s.z0);
     const long long lo = 1 - s.zg0, hi = (long long)p.nz - 1 - s.zg0;
@@ -1163,11 +1170,12 @@ int heat3d_step(heat3d_ctx* c, uint32_t nsteps)
     int rc = check_ctx(c);
     if (rc) return rc;
     if ((rc = begin_call(c))) return rc;
+    static const bool force_res = getenv("HEAT3D_DEBUG_FORCE_RES") != nullptr;   // experiments: time the residual-fused variant
     uint32_t left = nsteps;
     for (; c->variant2 && left >= 2; left -= 2)
-        if ((rc = step_block(c, 2, false))) return rc;
+        if ((rc = step_block(c, 2, force_res))) return rc;
     for (; left; --left)
-        if ((rc = step_block(c, 1, false))) return rc;
+        if ((rc = step_block(c, 1, force_res))) return rc;
     if (nsteps) c->have_res = false;
     return end_call(c);
 }
@@ -1202,6 +1210,77 @@ int heat3d_residual(heat3d_ctx* c, double* residual)
     return HEAT3D_OK;
 }
 
+// The reference's loop with the residual examined EVERY iteration, without idling the GPU between iterations:
+// iteration i+1 is queued before the host looks at the residual of iteration i (two residual slots, two events).
+// If iteration i turns out to be the converging one, iteration i+1 is simply dropped: a depth-1 step never touches
+// the buffer it read from, so flipping `cur` back restores the state after iteration i exactly.
+static int run_every_iteration(heat3d_ctx* c, uint32_t iter_max, double eps, uint32_t* fin, int32_t* conv, uint32_t* done)
+{
+    int rc = begin_call(c);
+    if (rc) return rc;
+    // Residual slot i&1: written by iteration i's kernels; then, on the COPY stream (so the compute stream goes
+    // straight on to iteration i+1), copied to the host and cleared for iteration i+2, which waits for that event.
+    for (Slab& s : c->slabs) {
+        if ((rc = set_dev(s))) return rc;
+        CU_TRY(cudaMemsetAsync(s.d_res_base, 0, 2 * sizeof(unsigned long long), s.compute));
+    }
+    c->res_slot_prezeroed = true;
+    auto issue = [&](uint32_t i) -> int {
+        const int slot = (int)(i & 1u);
+        for (Slab& s : c->slabs) {
+            int r0 = set_dev(s);
+            if (r0) return r0;
+            s.d_res = s.d_res_base + slot;
+            if (i >= 2) CU_TRY(cudaStreamWaitEvent(s.compute, s.ev_res[slot], 0));    // slot cleared after iteration i-2
+        }
+        int r = step_block(c, 1, true);
+        for (Slab& s : c->slabs) {
+            if (r) break;
+            if ((r = set_dev(s))) break;
+            CU_TRY(cudaEventRecord(s.ev_tmp, s.compute));
+            CU_TRY(cudaStreamWaitEvent(s.copy, s.ev_tmp, 0));
+            CU_TRY(cudaMemcpyAsync(s.h_scalar + 2 + slot, s.d_res, sizeof(double), cudaMemcpyDeviceToHost, s.copy));
+            CU_TRY(cudaMemsetAsync(s.d_res, 0, sizeof(unsigned long long), s.copy));
+            CU_TRY(cudaEventRecord(s.ev_res[slot], s.copy));
+        }
+        for (Slab& s : c->slabs) s.d_res = s.d_res_base;
+        return r;
+    };
+    double norm = 1.0;                                       // cu:325
+    uint32_t issued = 0;
+    if (iter_max && (rc = issue(issued++))) return rc;
+    for (uint32_t time = 0; time < iter_max; ++time) {
+        if (issued < iter_max && (rc = issue(issued++))) return rc;     // speculative next iteration
+        double res = 0.0;
+        for (Slab& s : c->slabs) {
+            if ((rc = set_dev(s))) return rc;
+            CU_TRY(cudaEventSynchronize(s.ev_res[time & 1u]));
+            if (s.h_scalar[2 + (time & 1u)] > res) res = s.h_scalar[2 + (time & 1u)];
+        }
+        if (res < DBL_MIN) res = DBL_MIN;                    // cu:1019
+        ++*done;
+        c->have_res = true;
+        c->last_res = res;
+        if (time == 0 && res != 0.0) norm = res;             // cu:1030-1032
+        if (res / norm < eps) {                              // cu:1055-1073
+            *conv = 1;
+            *fin = time;
+            if (issued > time + 1) {                         // drop the speculative iteration
+                if ((rc = heat3d_sync(c))) return rc;
+                c->cur ^= 1;
+                c->tm.steps -= 1;
+            }
+            break;
+        }
+    }
+    c->res_slot_prezeroed = false;
+    for (Slab& s : c->slabs) {      // later residual queries use slot 0 with their own clear on the compute stream
+        if ((rc = set_dev(s))) return rc;
+        CU_TRY(cudaStreamSynchronize(s.copy));
+    }
+    return end_call(c);
+}
+
 int heat3d_run(heat3d_ctx* c, uint32_t iter_max, double eps, uint32_t check_every, uint32_t* final_iters, int32_t* converged,
                uint32_t* applied)
 {
@@ -1212,6 +1291,10 @@ int heat3d_run(heat3d_ctx* c, uint32_t iter_max, double eps, uint32_t check_ever
     uint32_t fin = 0, done = 0;
     int32_t conv = 0;
     uint32_t time = 0;
+    if (check_every == 1 && !c->multi_process && c->snap_buf < 0) {
+        if ((rc = run_every_iteration(c, iter_max, eps, &fin, &conv, &done))) return rc;
+        time = iter_max;
+    }
     while (time < iter_max) {
         // next iteration index whose residual is examined: 0, then multiples of check_every (…-1), capped at the end
         uint32_t target = time == 0 ? 0 : ((time / check_every) + 1) * check_every - 1;

@@ -69,6 +69,16 @@ __device__ __forceinline__ double finish_z(double t, double c, double zm, double
     }
 }
 
+// rmax = max(rmax, |o - c|) on the bit patterns: one FP64 subtract, then integer compare/select on the ALU pipe (for
+// non-negative doubles the unsigned order of the bits is the order of the values), instead of a second FP64-pipe
+// operation per cell in a kernel whose sustained speed is set by the power the FP64 pipe draws.
+__device__ __forceinline__ void res_track(double& rmax, double o, double c)
+{
+    const unsigned long long b = (unsigned long long)__double_as_longlong(__dsub_rn(o, c)) & 0x7fffffffffffffffull;
+    const unsigned long long m = (unsigned long long)__double_as_longlong(rmax);
+    rmax = __longlong_as_double((long long)(b > m ? b : m));
+}
+
 // max over a warp of non-negative doubles, then one atomicMax on the bit pattern (order-preserving for >= 0).
 __device__ __forceinline__ void warp_residual_commit(double r, unsigned long long* slot)
 {
@@ -88,6 +98,25 @@ struct Geom {
     int za, zb;            // local output plane range [za, zb); every plane in it is a global interior plane
     double Dx, Dy, Dz;
 };
+
+// Same, one atomic per CTA: with ~65 000 warps per launch all hitting one address, per-warp atomics showed up as
+// 16 % of the kernel time at 512^3.  `scratch` is a shared-memory array of (blockDim/32) u64; every thread calls this.
+__device__ __forceinline__ void cta_residual_commit(double r, unsigned long long* slot, unsigned long long* scratch)
+{
+    unsigned long long b = (unsigned long long)__double_as_longlong(r);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, b, o);
+        b = other > b ? other : b;
+    }
+    if ((threadIdx.x & 31) == 0) scratch[threadIdx.x >> 5] = b;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int nw = (blockDim.x * blockDim.y + 31) / 32;
+        for (int i = 1; i < nw; ++i) b = scratch[i] > b ? scratch[i] : b;
+        if (b != 0ull) atomicMax(slot, b);
+    }
+}
 
 // ------------------------------------------------------------------------------------------------------
 // IC + Dirichlet shell (reference heat3D.cu:409-453), written to both buffers, ghost planes included.
@@ -140,7 +169,7 @@ __global__ void __launch_bounds__(256) stencil_baseline_kernel(const double* __r
             const double t = partial_xy<ARITH>(c, __ldg(p - 1), __ldg(p + 1), __ldg(p - g.pitch), __ldg(p + g.pitch), g.Dx, g.Dy);
             const double r = finish_z<ARITH>(t, c, below, above, g.Dz);
             *q = r;
-            if (RES) rmax = fmax(rmax, fabs(__dsub_rn(r, c)));
+            if (RES) res_track(rmax, r, c);
             below = c;
             c = above;
             p += g.plane;
@@ -276,15 +305,15 @@ __device__ __forceinline__ void plane_update(const double* __restrict__ S, int r
             double* o_ptr = out + (long long)r * pitch;
             if (sp.all) {
                 *(double2*)o_ptr = o;
-                if (RES) rmax = fmax(rmax, fmax(fabs(__dsub_rn(o.x, cp1[r].x)), fabs(__dsub_rn(o.y, cp1[r].y))));
+                if (RES) { res_track(rmax, o.x, cp1[r].x); res_track(rmax, o.y, cp1[r].y); }
             } else if ((sp.rows >> r) & 1u) {
                 if (sp.x0) {
                     o_ptr[0] = o.x;
-                    if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o.x, cp1[r].x)));
+                    if (RES) res_track(rmax, o.x, cp1[r].x);
                 }
                 if (sp.x1) {
                     o_ptr[1] = o.y;
-                    if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o.y, cp1[r].y)));
+                    if (RES) res_track(rmax, o.y, cp1[r].y);
                 }
             }
         }
@@ -441,7 +470,10 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
             release_stage(q);
         }
     }
-    if (RES) warp_residual_commit(rmax, res_slot);
+    if (RES) {
+        __syncthreads();                                      // every warp is done with the staged planes
+        cta_residual_commit(rmax, res_slot, (unsigned long long*)smem);
+    }
     if (is_end && w.done) signal_end_chunk(w);
 }
 

@@ -234,15 +234,15 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
                     double* o_ptr = out + (long long)r * g.pitch;
                     if (pl.st.all) {
                         *(double2*)o_ptr = o[r];
-                        if (RES) rmax = fmax(rmax, fmax(fabs(__dsub_rn(o[r].x, c1p1[r].x)), fabs(__dsub_rn(o[r].y, c1p1[r].y))));
+                        if (RES) { res_track(rmax, o[r].x, c1p1[r].x); res_track(rmax, o[r].y, c1p1[r].y); }
                     } else if ((pl.st.rows >> r) & 1u) {
                         if (pl.st.x0) {
                             o_ptr[0] = o[r].x;
-                            if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o[r].x, c1p1[r].x)));
+                            if (RES) res_track(rmax, o[r].x, c1p1[r].x);
                         }
                         if (pl.st.x1) {
                             o_ptr[1] = o[r].y;
-                            if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o[r].y, c1p1[r].y)));
+                            if (RES) res_track(rmax, o[r].y, c1p1[r].y);
                         }
                     }
                 }
@@ -290,15 +290,15 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
                 double* o_ptr = out + (long long)r * g.pitch;
                 if (pl.st.all) {
                     *(double2*)o_ptr = o[r];
-                    if (RES) rmax = fmax(rmax, fmax(fabs(__dsub_rn(o[r].x, c1p1[r].x)), fabs(__dsub_rn(o[r].y, c1p1[r].y))));
+                    if (RES) { res_track(rmax, o[r].x, c1p1[r].x); res_track(rmax, o[r].y, c1p1[r].y); }
                 } else if ((pl.st.rows >> r) & 1u) {
                     if (pl.st.x0) {
                         o_ptr[0] = o[r].x;
-                        if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o[r].x, c1p1[r].x)));
+                        if (RES) res_track(rmax, o[r].x, c1p1[r].x);
                     }
                     if (pl.st.x1) {
                         o_ptr[1] = o[r].y;
-                        if (RES) rmax = fmax(rmax, fabs(__dsub_rn(o[r].y, c1p1[r].y)));
+                        if (RES) res_track(rmax, o[r].y, c1p1[r].y);
                     }
                 }
             }
@@ -333,7 +333,10 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
         if (q + 1 < niter) H3_T2_BODY(q + 1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
     }
 #undef H3_T2_BODY
-    if (RES) warp_residual_commit(rmax, res_slot);
+    if (RES) {
+        __syncthreads();
+        cta_residual_commit(rmax, res_slot, (unsigned long long*)smem);
+    }
     if (is_end && w.done) signal_end_chunk(w);
 }
 

@@ -225,3 +225,25 @@ def test_multi_device_one_process_bitwise(h3, oracle, k):
         got = sim.download()
     assert np.array_equal(got, ref)
     assert res == oracle.residual(ref, _oracle_field(oracle, nx, ny, nz, nsteps - 1))
+
+
+@pytest.mark.parametrize("P", [1, 3])
+def test_run_every_iteration_is_exact_and_state_stays_consistent(h3, oracle, P):
+    """check_every=1 queues iteration i+1 before the host has seen residual i and drops it again on convergence:
+    iteration count, field and later stepping must be exactly the reference's."""
+    nx = ny = nz = 27
+    _, _, D = oracle.coefficients(nx, ny, nz)
+    with h3.Heat3D(nx, ny, nz, nslabs=P, devices=[0] * P) as sim:
+        sim.init_reference_field()
+        applied, fin, conv = sim.run(100000, 1e-6, check_every=1)
+        assert (applied, fin, conv) == (3303, 3302, True)
+        assert sim.timing()["steps"] == 3303
+        T = sim.download()
+        assert np.array_equal(T, _oracle_field(oracle, nx, ny, nz, 3303))
+        assert sim.residual() == oracle.residual(T, _oracle_field(oracle, nx, ny, nz, 3302))
+        sim.step(5)                                   # the dropped speculative iteration must leave no trace
+        assert np.array_equal(sim.download(), _oracle_field(oracle, nx, ny, nz, 3308))
+    with h3.Heat3D(nx, ny, nz, nslabs=P, devices=[0] * P) as sim:      # not converging: exactly iter_max updates
+        sim.init_reference_field()
+        assert sim.run(37, 1e-30, check_every=1) == (37, 0, False)
+        assert np.array_equal(sim.download(), _oracle_field(oracle, nx, ny, nz, 37))

@@ -200,18 +200,21 @@ T2Variant make_t2(const char* name)
 const std::vector<T2Variant>& t2_variants()
 {
     static const std::vector<T2Variant> v = {
+        // "_L" = schedule 1: only centre values live across iterations, which is what lets a thread own 4 rows inside
+        // 128 registers.  4 rows per thread = 12 % fewer shared-memory wavefronts per cell, the 64x32 region wastes
+        // less on the redundant ring (60x30 of 64x32 useful): +4 % at 512^3, +8 % at 1024^2 planes (sustained).
+        make_t2<64, 32, 4, 4, 2, 1>("t2_64x32_r4_s4_c2_L"),
+        make_t2<64, 32, 4, 3, 2, 1>("t2_64x32_r4_s3_c2_L"),
+        make_t2<64, 16, 4, 4, 3, 1>("t2_64x16_r4_s4_c3_L"),
+        make_t2<64, 16, 4, 5, 3, 1>("t2_64x16_r4_s5_c3_L"),
+        make_t2<64, 16, 4, 4, 4, 1>("t2_64x16_r4_s4_c4_L"),
+        make_t2<64, 16, 2, 4, 3, 1>("t2_64x16_r2_s4_c3_L"),
+        // schedule 0: partial_xy of the newest plane kept in registers (first version of the kernel)
         make_t2<64, 16, 2, 3, 2>("t2_64x16_r2_s3_c2"),
         make_t2<64, 16, 2, 4, 2>("t2_64x16_r2_s4_c2"),
         make_t2<64, 32, 2, 4, 1>("t2_64x32_r2_s4_c1"),
-        make_t2<64, 32, 2, 3, 1>("t2_64x32_r2_s3_c1"),
         make_t2<128, 16, 2, 4, 1>("t2_128x16_r2_s4_c1"),
-        make_t2<128, 16, 2, 3, 1>("t2_128x16_r2_s3_c1"),
         make_t2<128, 8, 2, 4, 2>("t2_128x8_r2_s4_c2"),
-        // "_L" = schedule 1 (only centre values live across iterations: 80 registers, 3 CTAs/SM).  Measured no faster
-        // than schedule 0 (profiles/r01_sweep_k2_sched1.txt): the kernel is bound by shared-memory wavefronts and FP64
-        // issue, not by latency that more resident warps could hide.
-        make_t2<64, 16, 2, 4, 3, 1>("t2_64x16_r2_s4_c3_L"),
-        make_t2<64, 16, 2, 3, 3, 1>("t2_64x16_r2_s3_c3_L"),
     };
     return v;
 }

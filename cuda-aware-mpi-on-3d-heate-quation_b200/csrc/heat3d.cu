@@ -204,6 +204,8 @@ const std::vector<T2Variant>& t2_variants()
         // 128 registers.  4 rows per thread = 12 % fewer shared-memory wavefronts per cell, the 64x32 region wastes
         // less on the redundant ring (60x30 of 64x32 useful): +4 % at 512^3, +8 % at 1024^2 planes (sustained).
         make_t2<64, 32, 4, 4, 2, 1>("t2_64x32_r4_s4_c2_L"),
+        make_t2<64, 32, 4, 4, 2, 2>("t2_64x32_r4_s4_c2_P"),
+        make_t2<64, 16, 4, 4, 3, 2>("t2_64x16_r4_s4_c3_P"),
         make_t2<64, 32, 4, 3, 2, 1>("t2_64x32_r4_s3_c2_L"),
         make_t2<64, 16, 4, 4, 3, 1>("t2_64x16_r4_s4_c3_L"),
         make_t2<64, 16, 4, 5, 3, 1>("t2_64x16_r4_s5_c3_L"),

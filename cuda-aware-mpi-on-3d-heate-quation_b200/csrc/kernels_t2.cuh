@@ -106,6 +106,7 @@ __device__ __forceinline__ void load_neighbours(const double* __restrict__ S, in
 // SCHED 1: nothing but centre values lives across iterations: a staged plane stays resident one iteration longer and
 //          the whole update of plane p-1 is formed when plane p has arrived (level 1), likewise for level 2 from the
 //          previous mid plane.  Same arithmetic, ~32 fewer registers per thread.
+// SCHED 2: schedule 1 with the mid plane stored split by x parity (cheaper x-neighbour loads at level 2).
 template <int CX, int CY, int RY, int STAGES, int ARITH, bool RES, int MINB, int SCHED>
 __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     stencil_tma_t2_kernel(const __grid_constant__ CUtensorMap tmap, double* __restrict__ dst, Geom g, TmaWork w, int z1lo, int z1hi,
@@ -120,7 +121,7 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
 #else
     constexpr bool SHFL_X = false;
 #endif
-    static_assert(CX % 64 == 0 && CY % RY == 0 && NTHR % 32 == 0 && NTHR <= 1024 && STAGES >= 2 + SCHED, "tile shape");
+    static_assert(CX % 64 == 0 && CY % RY == 0 && NTHR % 32 == 0 && NTHR <= 1024 && STAGES >= 2 + (SCHED ? 1 : 0), "tile shape");
 
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* mid = smem + STAGES * Cfg::STAGE_STRIDE;
@@ -174,6 +175,12 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     pl.st.all = pl.st.x0 && pl.st.x1 && pl.st.rows == (1u << RY) - 1u;
     double* out = dst + (long long)zs * g.plane + (long long)gy * g.pitch + gx;
     const int soff = (1 + ry * RY) * ROW + 2 + 2 * lx;
+    // SCHED 2 stores the mid plane split by x parity: a thread's left / right x neighbours are then 8-byte words at
+    // consecutive lanes (2 wavefronts per warp load) instead of the second halves of 16-byte pairs (4 wavefronts).
+    constexpr int MP = CX / 2 + 2;                       // words per row of one parity array (one halo pair each side)
+    constexpr int MHALF = (CY + 2) * MP;                 // one parity array; two of them fit one STAGE_STRIDE
+    static_assert(2 * MHALF * 8 <= Cfg::STAGE_STRIDE, "split mid plane must fit the mid buffer");
+    const int moff = (1 + ry * RY) * MP + 1 + lx;
     double rmax = 0.0;
 
     double2 C0[3][RY], t0[RY], tw0[RY];      // level 0: centres of the last three planes, partial / 2*centre of the newest
@@ -276,13 +283,35 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
                     if (!(row && pl.i1x1)) c1n[r].y = c0p1[r].y;
                 }
             }
-            double* M = (double*)(mid + par * Cfg::STAGE_STRIDE) + soff;
+            if (SCHED == 2) {   // even-x cells and odd-x cells in separate arrays (see MP below)
+                double* ME = (double*)(mid + par * Cfg::STAGE_STRIDE) + moff;
+                double* MO = ME + MHALF;
 #pragma unroll
-            for (int r = 0; r < RY; ++r) *(double2*)(M + r * ROW) = c1n[r];
+                for (int r = 0; r < RY; ++r) {
+                    ME[r * MP] = c1n[r].x;
+                    MO[r * MP] = c1n[r].y;
+                }
+            } else {
+                double* M = (double*)(mid + par * Cfg::STAGE_STRIDE) + soff;
+#pragma unroll
+                for (int r = 0; r < RY; ++r) *(double2*)(M + r * ROW) = c1n[r];
+            }
         }
         if (q >= 4) {   // level 2: local plane zs + q - 4, from the mid plane published one iteration ago
-            const double* Mp = (const double*)(mid + (par ^ 1) * Cfg::STAGE_STRIDE) + soff;
-            load_neighbours<RY, false>(Mp, ROW, c1p1, lane, xl, xr, up, dn);
+            if (SCHED == 2) {
+                const double* ME = (const double*)(mid + (par ^ 1) * Cfg::STAGE_STRIDE) + moff;
+                const double* MO = ME + MHALF;
+                up = make_double2(ME[-MP], MO[-MP]);
+                dn = make_double2(ME[RY * MP], MO[RY * MP]);
+#pragma unroll
+                for (int r = 0; r < RY; ++r) {
+                    xl[r] = MO[r * MP - 1];      // the odd cell of the pair to the left: consecutive lanes, consecutive words
+                    xr[r] = ME[r * MP + 1];      // the even cell of the pair to the right
+                }
+            } else {
+                const double* Mp = (const double*)(mid + (par ^ 1) * Cfg::STAGE_STRIDE) + soff;
+                load_neighbours<RY, false>(Mp, ROW, c1p1, lane, xl, xr, up, dn);
+            }
             double2 o[RY];
             level_full<RY, ARITH>(c1p1, xl, xr, up, dn, c1p2, c1n, o, g.Dx, g.Dy, g.Dz);
 #pragma unroll
@@ -316,7 +345,7 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     // Register rotation: level 0 newest = C0[q % 3]; level 1 newest (plane q-1 of the run) = C1[(q + 2) % 3].
 #define H3_T2_BODY(qq, a, b, c, d, e, f)                                  \
     do {                                                                  \
-        if (SCHED == 1) body1(qq, a, b, c, d, e, f);                      \
+        if (SCHED >= 1) body1(qq, a, b, c, d, e, f);                      \
         else body(qq, a, b, c, d, e, f);                                  \
     } while (0)
     H3_T2_BODY(0, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);

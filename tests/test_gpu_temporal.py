@@ -10,7 +10,7 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 # cx,cy,rows/thread,stages,CTAs/SM[,chunk_len,schedule]
-T2_TUNES = ["64,32,4,4,2,7,1", "64,32,4,3,2,7,1", "64,16,4,4,3,7,1", "64,16,4,5,3,7,1", "64,16,4,4,4,7,1", "64,16,2,4,3,7,1",
+T2_TUNES = ["64,32,4,4,2,7,2", "64,16,4,4,3,7,2", "64,32,4,4,2,7,1", "64,32,4,3,2,7,1", "64,16,4,4,3,7,1", "64,16,4,5,3,7,1", "64,16,4,4,4,7,1", "64,16,2,4,3,7,1",
             "64,16,2,3,2", "64,16,2,4,2", "64,32,2,4,1", "128,16,2,4,1", "128,8,2,4,2"]
 
 
@@ -55,7 +55,7 @@ def test_every_depth2_variant(h3, oracle, tune):
     ref = _oracle_field(oracle, nx, ny, nz, nsteps)
     prev = _oracle_field(oracle, nx, ny, nz, nsteps - 1)
     with h3.Heat3D(nx, ny, nz, temporal_k=2) as sim:
-        assert sim.kernel_name() == "t2_%sx%s_r%s_s%s_c%s" % tuple(f[:5]) + ("_L" if len(f) > 6 and f[6] == "1" else "")
+        assert sim.kernel_name() == "t2_%sx%s_r%s_s%s_c%s" % tuple(f[:5]) + ({"1": "_L", "2": "_P"}.get(f[6], "") if len(f) > 6 else "")
         sim.init_reference_field()
         res = sim.step_residual(nsteps)               # even count: the residual comes out of the depth-2 kernel
         got = sim.download()

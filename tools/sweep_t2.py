@@ -24,7 +24,7 @@ cells = (shape[0] - 2) * (shape[1] - 2) * (shape[2] - 2)
 for arith in ((0,) if os.environ.get("SWEEP_STRICT_ONLY") else (0, 1)):
     for tune in TUNES:
         for ch in CHUNKS:
-            base, sched = (tune[:-1], 1) if tune.endswith("L") else (tune, 0)
+            base, sched = (tune[:-1], 1) if tune.endswith("L") else (tune[:-1], 2) if tune.endswith("P") else (tune, 0)
             os.environ["HEAT3D_T2_TUNE"] = f"{base},{ch},{sched}"
             try:
                 with h3.Heat3D(*shape, arith=arith, temporal_k=2) as sim:

@@ -21,6 +21,7 @@
 namespace {
 
 constexpr uint32_t HALO_RING = 256;
+constexpr uint32_t GRAPH_BLOCKS = 32;   // even: the current-buffer index is the same before and after a graph launch
 thread_local char g_err[512] = "";
 
 int fail(int code, const char* fmt, ...)
@@ -277,6 +278,10 @@ struct heat3d_ctx {
     double last_res = 0.0;
     heat3d_timing tm;
     bool halo_timed = false;
+    // CUDA graphs of GRAPH_BLOCKS consecutive passes of a single-slab context, one per (depth index, buffer parity):
+    // small grids are launch-bound, and a graph launch costs about as much as one kernel launch
+    cudaGraphExec_t step_graph[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
+    bool graphs_ok = true;
     bool res_slot_prezeroed = false;   // pipelined convergence loop: residual slots are cleared off the compute stream
     bool end_signal = false;           // stream memory operations available: single-launch steps with end-chunk signalling
     unsigned long long seq = 0;        // number of ghost exchanges issued so far (same on every process)
@@ -1025,6 +1030,9 @@ int heat3d_destroy(heat3d_ctx* c)
         cudaSetDevice(s.dev);
         if (g_nccl.AllReduce(s.d_scalar, s.d_scalar + 1, 1, ncclFloat64, ncclSum, s.nccl, s.comm) == ncclSuccess) cudaStreamSynchronize(s.comm);
     }
+    for (auto& row : c->step_graph)
+        for (cudaGraphExec_t& g : row)
+            if (g) { cudaGraphExecDestroy(g); g = nullptr; }
     for (Slab& s : c->slabs) destroy_slab(s);
     delete c;
     return HEAT3D_OK;
@@ -1170,17 +1178,66 @@ int heat3d_download(heat3d_ctx* c, double* host_global)
     return heat3d_download_planes(c, host_global + (size_t)z0 * c->p.nx * c->p.ny, z0, z1 - z0);
 }
 
+// GRAPH_BLOCKS passes of depth k as one graph launch (single-slab contexts only; captured on first use).
+static int step_graph_blocks(heat3d_ctx* c, int k)
+{
+    Slab& s = c->slabs[0];
+    cudaGraphExec_t& exec = c->step_graph[k - 1][c->cur];
+    if (!exec) {
+        const uint64_t steps0 = c->tm.steps, launches0 = c->tm.launches, lc0 = c->tm.last_call_launches,
+                       ls0 = c->tm.last_call_stencil_launches;
+        const uint32_t cs0 = c->call_steps;
+        cudaGraph_t graph = nullptr;
+        if (cudaStreamBeginCapture(s.compute, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return 1; }
+        int rc = HEAT3D_OK;
+        for (uint32_t i = 0; i < GRAPH_BLOCKS && !rc; ++i) rc = step_block(c, k, false);
+        const cudaError_t e = cudaStreamEndCapture(s.compute, &graph);
+        // capture only records work: undo the bookkeeping the recording did
+        c->tm.steps = steps0; c->tm.launches = launches0; c->tm.last_call_launches = lc0; c->tm.last_call_stencil_launches = ls0;
+        c->call_steps = cs0;
+        if (rc || e != cudaSuccess || !graph) { cudaGetLastError(); if (graph) cudaGraphDestroy(graph); return 1; }
+        const cudaError_t ei = cudaGraphInstantiate(&exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ei != cudaSuccess) { cudaGetLastError(); exec = nullptr; return 1; }
+    }
+    CU_TRY(cudaGraphLaunch(exec, s.compute));
+    c->tm.steps += (uint64_t)k * GRAPH_BLOCKS;
+    c->tm.launches += GRAPH_BLOCKS;
+    c->tm.last_call_launches += GRAPH_BLOCKS;
+    c->tm.last_call_stencil_launches += GRAPH_BLOCKS;
+    c->call_steps += GRAPH_BLOCKS;
+    return HEAT3D_OK;
+}
+
+// `nsteps` plain updates (no residual): graph replays while whole graphs fit, then depth-2 passes, then single steps.
+static int advance_plain(heat3d_ctx* c, uint32_t nsteps)
+{
+    static const bool force_res = getenv("HEAT3D_DEBUG_FORCE_RES") != nullptr;   // experiments: time the residual-fused variant
+    static const bool no_graphs = getenv("HEAT3D_NO_GRAPHS") != nullptr;
+    int rc = HEAT3D_OK;
+    uint32_t left = nsteps;
+    if (c->slabs.size() == 1 && !c->multi_process && c->use_tma && c->graphs_ok && !no_graphs && !force_res && c->snap_buf < 0) {
+        const int k = c->variant2 ? 2 : 1;
+        while (left >= (uint32_t)k * GRAPH_BLOCKS) {
+            const int g = step_graph_blocks(c, k);
+            if (g == 1) { c->graphs_ok = false; break; }     // capture not possible here: plain launches from now on
+            if (g) return g;
+            left -= (uint32_t)k * GRAPH_BLOCKS;
+        }
+    }
+    for (; c->variant2 && left >= 2; left -= 2)
+        if ((rc = step_block(c, 2, force_res))) return rc;
+    for (; left; --left)
+        if ((rc = step_block(c, 1, force_res))) return rc;
+    return HEAT3D_OK;
+}
+
 int heat3d_step(heat3d_ctx* c, uint32_t nsteps)
 {
     int rc = check_ctx(c);
     if (rc) return rc;
     if ((rc = begin_call(c))) return rc;
-    static const bool force_res = getenv("HEAT3D_DEBUG_FORCE_RES") != nullptr;   // experiments: time the residual-fused variant
-    uint32_t left = nsteps;
-    for (; c->variant2 && left >= 2; left -= 2)
-        if ((rc = step_block(c, 2, force_res))) return rc;
-    for (; left; --left)
-        if ((rc = step_block(c, 1, force_res))) return rc;
+    if ((rc = advance_plain(c, nsteps))) return rc;
     if (nsteps) c->have_res = false;
     return end_call(c);
 }
@@ -1193,13 +1250,8 @@ int heat3d_step_residual(heat3d_ctx* c, uint32_t nsteps, double* residual)
     if (nsteps == 0) return fail(HEAT3D_ERR_INVALID, "nsteps must be >= 1 to produce a residual");
     if ((rc = begin_call(c))) return rc;
     // all but the last block plain; the last block (2 updates if that leaves an even count, else 1) carries the residual
-    uint32_t left = nsteps;
-    const uint32_t last = (c->variant2 && left >= 2 && left % 2 == 0) ? 2u : 1u;
-    left -= last;
-    for (; c->variant2 && left >= 2; left -= 2)
-        if ((rc = step_block(c, 2, false))) return rc;
-    for (; left; --left)
-        if ((rc = step_block(c, 1, false))) return rc;
+    const uint32_t last = (c->variant2 && nsteps >= 2 && nsteps % 2 == 0) ? 2u : 1u;
+    if ((rc = advance_plain(c, nsteps - last))) return rc;
     if ((rc = step_block(c, (int)last, true))) return rc;
     if ((rc = end_call(c))) return rc;
     return fetch_residual(c, residual);

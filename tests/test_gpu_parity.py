@@ -247,3 +247,19 @@ def test_run_every_iteration_is_exact_and_state_stays_consistent(h3, oracle, P):
         sim.init_reference_field()
         assert sim.run(37, 1e-30, check_every=1) == (37, 0, False)
         assert np.array_equal(sim.download(), _oracle_field(oracle, nx, ny, nz, 37))
+
+
+@pytest.mark.parametrize("k", [1, 2])
+def test_long_runs_through_cuda_graphs(h3, oracle, k):
+    """heat3d_step replays graphs of 32 passes on single-slab contexts; odd leftovers take plain launches."""
+    nx, ny, nz, nsteps = 40, 33, 29, 2 * 32 * k + 32 * k + 7          # three graph launches and a remainder
+    ref = _oracle_field(oracle, nx, ny, nz, nsteps)
+    with h3.Heat3D(nx, ny, nz, temporal_k=k) as sim:
+        sim.init_reference_field()
+        sim.step(nsteps)
+        t = sim.timing()
+        assert t["steps"] == nsteps
+        assert np.array_equal(sim.download(), ref)
+        sim.step(1)                                    # buffer parity flipped: the other graph gets built next
+        sim.step(32 * k)
+        assert np.array_equal(sim.download(), _oracle_field(oracle, nx, ny, nz, nsteps + 1 + 32 * k))

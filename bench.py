@@ -299,7 +299,7 @@ def main():
                 "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": scaling,
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic (reference IC/BC: zero interior, linear-in-y Dirichlet shell)",
                 "config": {"workload": wname, "grid": [nx, ny, nz], "updates_per_step": tsteps, "arith": args.arith, "temporal_k": k,
-                           "decomposition": f"{n} z-slab(s), one process per GPU" + (", ghost planes by NCCL send/recv overlapped with interior compute" if n > 1 else ""),
+                           "decomposition": f"{n} z-slab(s), one process per GPU" + (f", ghost planes by {sim.exchange_name()} overlapped with interior compute" if n > 1 else ""),
                            "l2": "inputs exceed L2 (two %.1f GiB buffers per GPU vs 126 MB)" % ((z1 - z0) * ny * nx * 8 / 2**30)},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
                 "wall_ms_per_step": wall_ms / args.steps, "snapshots": {"count": nsnap, "bytes_each_per_rank": int(snap_buf.nbytes)} if snap_buf is not None else None,

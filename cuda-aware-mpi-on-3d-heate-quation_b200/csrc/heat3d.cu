@@ -251,6 +251,9 @@ struct Slab {
     // cross-process neighbours reached through CUDA IPC (side 0 = lower, 1 = upper): their two field buffers and
     // their arrival flags mapped into this process, plus this slab's own flags {written by lower, written by upper}
     bool ipc = false;
+    bool peer_is_ipc[2] = {false, false};      // peer_buf/peer_flags of that side came from cudaIpcOpenMemHandle
+    unsigned long long* d_side_done = nullptr;  // peer-store exchange: finished end-chunk CTAs per side {lower, upper}
+    unsigned long long side_target[2] = {0, 0};
     double* peer_buf[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
     unsigned long long* peer_flags[2] = {nullptr, nullptr};
     unsigned long long* d_flags = nullptr;
@@ -283,6 +286,7 @@ struct heat3d_ctx {
     cudaGraphExec_t step_graph[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};
     bool graphs_ok = true;
     bool res_slot_prezeroed = false;   // pipelined convergence loop: residual slots are cleared off the compute stream
+    bool store_mode = false;           // ghost planes are written by the stencil kernel itself into the neighbours' memory
     bool end_signal = false;           // stream memory operations available: single-launch steps with end-chunk signalling
     unsigned long long seq = 0;        // number of ghost exchanges issued so far (same on every process)
     bool timing_pending = false;       // a call's ev_start/ev_stop have not been folded into tm yet
@@ -316,22 +320,46 @@ int make_tmap(Slab& s, CUtensorMap* map, int which, const heat3d_ctx* c, int box
 // Cuts output planes [za, zb) into an optional short end chunk per side whose neighbour is waiting (ends bit 0 =
 // lower, bit 1 = upper) plus uniform middle chunks; returns the grid size and books the end-chunk CTAs on the
 // slab's completion counter.
-long long plan_chunks(h3::TmaWork& w, int za, int zb, int ends, int end_len, int chunk_len, long long slots, Slab& s)
+// Peer-store exchange: for side 0 (lower) / 1 (upper), where this slab's outer G planes go in the neighbour's memory.
+struct MirrorInfo {
+    double* base[2];                  // neighbour address of local plane z0[side] (row 0, column 0); nullptr = side off
+    int z0[2], z1[2];
+    unsigned long long* flag[2];
+    unsigned long long flag_value;
+};
+
+long long plan_chunks(h3::TmaWork& w, int za, int zb, int ends, int end_len, int chunk_len, long long slots, Slab& s,
+                      const MirrorInfo* mi = nullptr)
 {
     const long long ntiles = (long long)w.ntx * w.nty;
     w.n_end = 0;
     w.mid_za = za;
     w.mid_zb = zb;
-    w.done = ends ? s.d_done : nullptr;
-    for (int i = 0; i < 2; ++i) w.end_za[i] = w.end_zb[i] = 0;
+    w.done = (ends && !mi) ? s.d_done : nullptr;
+    w.flag_value = mi ? mi->flag_value : 0;
+    for (int i = 0; i < 2; ++i) {
+        w.end_za[i] = w.end_zb[i] = 0;
+        w.mirror[i] = nullptr; w.mirror_z0[i] = w.mirror_z1[i] = 0;
+        w.side_done[i] = nullptr; w.side_goal[i] = 0; w.peer_flag[i] = nullptr;
+    }
+    if (ends == 3) end_len = std::max((int)s.G, std::min(end_len, (zb - za) / 2));   // thin slabs: the two end chunks must not meet
+    auto mirror_side = [&](int side) {
+        if (!mi || !mi->base[side]) return;
+        const int i = w.n_end;
+        w.mirror[i] = mi->base[side]; w.mirror_z0[i] = mi->z0[side]; w.mirror_z1[i] = mi->z1[side];
+        s.side_target[side] += (unsigned long long)ntiles;
+        w.side_done[i] = s.d_side_done + side; w.side_goal[i] = s.side_target[side]; w.peer_flag[i] = mi->flag[side];
+    };
     if ((ends & 1) && w.mid_zb > w.mid_za) {
         const int e = std::min(end_len, w.mid_zb - w.mid_za);
         w.end_za[w.n_end] = w.mid_za; w.end_zb[w.n_end] = w.mid_za + e;
+        mirror_side(0);
         w.mid_za += e; w.n_end++;
     }
     if ((ends & 2) && w.mid_zb > w.mid_za) {
         const int e = std::min(end_len, w.mid_zb - w.mid_za);
         w.end_za[w.n_end] = w.mid_zb - e; w.end_zb[w.n_end] = w.mid_zb;
+        mirror_side(1);
         w.mid_zb -= e; w.n_end++;
     }
     const int nzp = w.mid_zb - w.mid_za;
@@ -345,8 +373,29 @@ long long plan_chunks(h3::TmaWork& w, int za, int zb, int ends, int end_len, int
         w.chunk_len = (int)((nzp + nch - 1) / nch);
         nch = (nzp + w.chunk_len - 1) / w.chunk_len;
     }
-    if (ends) s.done_target += (unsigned long long)ntiles * w.n_end;
+    if (ends && !mi) s.done_target += (unsigned long long)ntiles * w.n_end;
     return ntiles * (w.n_end + nch);
+}
+
+// Where slab s's outer G planes of buffer `dstb` live in its neighbours' memory (peer-store exchange).
+bool fill_mirror(const heat3d_ctx* c, const Slab& s, int dstb, int ends, MirrorInfo& mi)
+{
+    if (!c->store_mode || !ends) return false;
+    const uint32_t nzl = s.z1 - s.z0;
+    for (int side = 0; side < 2; ++side) { mi.base[side] = nullptr; mi.z0[side] = mi.z1[side] = 0; mi.flag[side] = nullptr; }
+    mi.flag_value = c->seq;
+    if ((ends & 1) && s.lower) {       // my first G owned planes -> the lower neighbour's upper ghost planes
+        const uint32_t n_nzl = (uint32_t)((uint64_t)s.gidx * c->p.nz / c->p.nslabs) - (uint32_t)((uint64_t)(s.gidx - 1) * c->p.nz / c->p.nslabs);
+        mi.base[0] = s.peer_buf[0][dstb] + (long long)(s.G + n_nzl) * s.plane;
+        mi.z0[0] = (int)s.G; mi.z1[0] = (int)(2 * s.G);
+        mi.flag[0] = s.peer_flags[0] + 1;
+    }
+    if ((ends & 2) && s.upper) {       // my last G owned planes -> the upper neighbour's lower ghost planes
+        mi.base[1] = s.peer_buf[1][dstb];
+        mi.z0[1] = (int)nzl; mi.z1[1] = (int)(nzl + s.G);
+        mi.flag[1] = s.peer_flags[1] + 0;
+    }
+    return true;
 }
 
 // One stencil launch over local output planes [za, zb) of slab s, reading buffer `src`.
@@ -366,8 +415,10 @@ int launch_stencil(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res, in
         // z-chunks: short chunks (default 16 output planes, tune[5] overrides) make the grid sweep the domain
         // z-major, wave after wave, so the planes a wave touches - and the halos its tiles share - stay in L2;
         // but never fewer chunks than it takes to fill every resident CTA slot once.
+        MirrorInfo mi;
+        const bool mirrored = fill_mirror(c, s, src ^ 1, ends, mi);
         const long long grid = plan_chunks(w, za, zb, ends, /*end_len=*/8, c->p.tune[5] > 0 ? c->p.tune[5] : 16,
-                                           (long long)s.num_sms * v.minb, s);
+                                           (long long)s.num_sms * v.minb, s, mirrored ? &mi : nullptr);
         void* args[] = {(void*)&s.tmap[src], (void*)&dst, (void*)&g, (void*)&w, (void*)&s.d_res};
         CU_TRY(cudaLaunchKernel(v.fn[ar][res ? 1 : 0], dim3((unsigned)grid), dim3(v.threads), args, v.smem, s.compute));
     } else {
@@ -407,7 +458,9 @@ int launch_stencil_t2(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res,
     h3::TmaWork w;
     w.ntx = ((int)c->p.nx + (v.cx - 4) - 1) / (v.cx - 4);
     w.nty = ((int)c->p.ny + (v.cy - 2) - 1) / (v.cy - 2);
-    const long long grid = plan_chunks(w, za, zb, ends, /*end_len=*/16, c->t2_chunk, (long long)s.num_sms * v.minb, s);
+    MirrorInfo mi;
+    const bool mirrored = fill_mirror(c, s, src ^ 1, ends, mi);
+    const long long grid = plan_chunks(w, za, zb, ends, /*end_len=*/16, c->t2_chunk, (long long)s.num_sms * v.minb, s, mirrored ? &mi : nullptr);
     int z1lo = (int)(1 - s.zg0), z1hi = (int)((long long)c->p.nz - 1 - s.zg0);   // level-1 planes that are global interior planes
     void* args[] = {(void*)&s.tmap2[src], (void*)&dst, (void*)&g, (void*)&w, (void*)&z1lo, (void*)&z1hi, (void*)&s.d_res};
     CU_TRY(cudaLaunchKernel(v.fn[ar][res ? 1 : 0], dim3((unsigned)grid), dim3(v.threads), args, v.smem, s.compute));
@@ -429,6 +482,7 @@ Slab* local_slab(heat3d_ctx* c, int gidx)
 int exchange_ghosts(heat3d_ctx* c, int b, bool after_counted_launch = false)
 {
     bool any_nccl = false;
+    c->seq++;
     for (Slab& s : c->slabs) {
         if (!s.lower && !s.upper) continue;
         int rc = set_dev(s);
@@ -446,6 +500,10 @@ int exchange_ghosts(heat3d_ctx* c, int b, bool after_counted_launch = false)
                 const double* from = s.buf[b] + (long long)s.G * s.plane;
                 double* to = n->buf[b] + (long long)(n->G + (n->z1 - n->z0)) * n->plane;
                 CU_TRY(cudaMemcpyPeerAsync(to, n->dev, from, s.dev, bytes, s.comm));
+                if (c->store_mode) {   // keep the arrival-flag chain the kernels use consistent
+                    CUresult r = g_stream_write64((CUstream)s.comm, (CUdeviceptr)(n->d_flags + 1), c->seq, 0);
+                    if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuStreamWriteValue64 failed with CUresult %d", (int)r);
+                }
             } else any_nccl = true;
         }
         if (s.upper) {
@@ -453,10 +511,13 @@ int exchange_ghosts(heat3d_ctx* c, int b, bool after_counted_launch = false)
                 const double* from = s.buf[b] + (long long)nzl * s.plane;
                 double* to = n->buf[b];
                 CU_TRY(cudaMemcpyPeerAsync(to, n->dev, from, s.dev, bytes, s.comm));
+                if (c->store_mode) {
+                    CUresult r = g_stream_write64((CUstream)s.comm, (CUdeviceptr)(n->d_flags + 0), c->seq, 0);
+                    if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuStreamWriteValue64 failed with CUresult %d", (int)r);
+                }
             } else any_nccl = true;
         }
     }
-    c->seq++;
     if (any_nccl && c->slabs[0].ipc) {
         // one-sided puts into the neighbour process's ghost planes by the copy engines, then a flag write that is
         // ordered after the copy in the stream: no SM is needed while the interior kernel owns them all
@@ -504,22 +565,18 @@ int exchange_ghosts(heat3d_ctx* c, int b, bool after_counted_launch = false)
 }
 
 // Make slab s's compute stream wait until its ghost planes (filled by the previous exchange) have landed.
-int wait_ghosts(heat3d_ctx* c, Slab& s)
+int wait_ghosts(heat3d_ctx* c, Slab& s, unsigned long long seq)
 {
-    // own ev_put: my previous sends have left my planes; neighbour's ev_put / flag: its planes have landed in my ghosts
-    if (s.lower) {
-        Slab* n = local_slab(c, s.gidx - 1);
-        CU_TRY(cudaStreamWaitEvent(s.compute, n ? n->ev_put : s.ev_put, 0));
-        if (!n && s.ipc && c->seq) {
-            CUresult r = g_stream_wait64((CUstream)s.compute, (CUdeviceptr)(s.d_flags + 0), c->seq, CU_STREAM_WAIT_VALUE_GEQ);
-            if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuStreamWaitValue64 failed with CUresult %d", (int)r);
+    for (int side = 0; side < 2; ++side) {
+        if (!(side == 0 ? s.lower : s.upper)) continue;
+        Slab* n = local_slab(c, s.gidx + (side == 0 ? -1 : 1));
+        if (!c->store_mode) {
+            // own ev_put: my previous sends have left my planes; neighbour's ev_put: its planes have landed in my ghosts
+            CU_TRY(cudaStreamWaitEvent(s.compute, n ? n->ev_put : s.ev_put, 0));
+            if (n || !s.ipc) continue;
         }
-    }
-    if (s.upper) {
-        Slab* n = local_slab(c, s.gidx + 1);
-        CU_TRY(cudaStreamWaitEvent(s.compute, n ? n->ev_put : s.ev_put, 0));
-        if (!n && s.ipc && c->seq) {
-            CUresult r = g_stream_wait64((CUstream)s.compute, (CUdeviceptr)(s.d_flags + 1), c->seq, CU_STREAM_WAIT_VALUE_GEQ);
+        if (seq) {   // arrival flag written by the neighbour (its kernel in store mode, its exchange stream otherwise)
+            CUresult r = g_stream_wait64((CUstream)s.compute, (CUdeviceptr)(s.d_flags + side), seq, CU_STREAM_WAIT_VALUE_GEQ);
             if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuStreamWaitValue64 failed with CUresult %d", (int)r);
         }
     }
@@ -535,6 +592,8 @@ int step_block(heat3d_ctx* c, int k, bool res)
     const int src = c->cur, dst = c->cur ^ 1;
     const bool overlap = !(c->p.flags & HEAT3D_FLAG_NO_OVERLAP);
     bool counted = false;
+    const unsigned long long seq_before = c->seq;       // ghosts of `src` arrived with this sequence number
+    if (c->store_mode) c->seq++;                        // the number this pass's kernels publish
     for (Slab& s : c->slabs) {
         int rc = set_dev(s);
         if (rc) return rc;
@@ -545,8 +604,14 @@ int step_block(heat3d_ctx* c, int k, bool res)
             continue;
         }
         if (c->halo_timed) CU_TRY(cudaEventRecord(s.ev_wait0[c->call_steps % HALO_RING], s.compute));
-        if ((rc = wait_ghosts(c, s))) return rc;
+        if ((rc = wait_ghosts(c, s, seq_before))) return rc;
         if (c->halo_timed) CU_TRY(cudaEventRecord(s.ev_wait1[c->call_steps % HALO_RING], s.compute));
+        if (c->store_mode) {
+            // ONE launch and nothing else: the end chunks write their outer planes straight into the neighbours' ghost
+            // planes and the last CTA of each publishes this pass's sequence number in the neighbour's arrival flag
+            if ((rc = launch(s, src, s.za, s.zb, res, (s.lower ? 1 : 0) | (s.upper ? 2 : 0)))) return rc;
+            continue;
+        }
         if (overlap && c->use_tma && c->end_signal) {
             // ONE launch: the chunks next to a neighbour run first and count themselves done on s.d_done; the exchange
             // stream waits for that count, so the ghost planes leave while this kernel works on the rest of the slab
@@ -569,7 +634,7 @@ int step_block(heat3d_ctx* c, int k, bool res)
         if (!overlap) CU_TRY(cudaEventRecord(s.ev_boundary, s.compute));
     }
     if (c->snap_buf == dst) c->snap_buf = -1;
-    if (c->slabs.size() > 1 || c->multi_process) {
+    if (!c->store_mode && (c->slabs.size() > 1 || c->multi_process)) {
         int rc = exchange_ghosts(c, dst, counted);
         if (rc) return rc;
     }
@@ -666,11 +731,13 @@ void destroy_slab(Slab& s)
 {
     cudaSetDevice(s.dev);
     for (int side = 0; side < 2; ++side) {
+        if (!s.peer_is_ipc[side]) continue;
         for (int b = 0; b < 2; ++b)
             if (s.peer_buf[side][b]) cudaIpcCloseMemHandle(s.peer_buf[side][b]);
         if (s.peer_flags[side]) cudaIpcCloseMemHandle(s.peer_flags[side]);
     }
     if (s.d_flags) cudaFree(s.d_flags);
+    if (s.d_side_done) cudaFree(s.d_side_done);
     if (s.nccl && g_nccl.CommDestroy) g_nccl.CommDestroy(s.nccl);
     for (int b = 0; b < 2; ++b)
         if (s.buf[b]) cudaFree(s.buf[b]);
@@ -737,6 +804,10 @@ int setup_slab(heat3d_ctx* c, Slab& s)
     for (cudaEvent_t& e : s.ev_res) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     CU_TRY(cudaMalloc(&s.d_done, sizeof(unsigned long long)));
     CU_TRY(cudaMemset(s.d_done, 0, sizeof(unsigned long long)));
+    CU_TRY(cudaMalloc(&s.d_side_done, 2 * sizeof(unsigned long long)));
+    CU_TRY(cudaMemset(s.d_side_done, 0, 2 * sizeof(unsigned long long)));
+    CU_TRY(cudaMalloc(&s.d_flags, 2 * sizeof(unsigned long long)));
+    CU_TRY(cudaMemset(s.d_flags, 0, 2 * sizeof(unsigned long long)));
     CU_TRY(cudaMemset(s.d_res_base, 0, 2 * sizeof(unsigned long long)));
     s.partial_blocks = s.num_sms * 8;
     CU_TRY(cudaMalloc(&s.d_partial, (size_t)s.partial_blocks * sizeof(double)));
@@ -784,8 +855,6 @@ int setup_ipc(heat3d_ctx* c, bool want)
     struct Handles { cudaIpcMemHandle_t buf[2], flags; };
     const int P = c->p.nslabs;
     bool ok = want && load_stream_memops() == HEAT3D_OK;
-    CU_TRY(cudaMalloc(&s.d_flags, 2 * sizeof(unsigned long long)));
-    CU_TRY(cudaMemset(s.d_flags, 0, 2 * sizeof(unsigned long long)));
     Handles mine;
     memset(&mine, 0, sizeof mine);
     if (ok) {
@@ -807,6 +876,7 @@ int setup_ipc(heat3d_ctx* c, bool want)
             for (int b = 0; b < 2 && ok; ++b)
                 ok = cudaIpcOpenMemHandle((void**)&s.peer_buf[side][b], all[n].buf[b], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
             if (ok) ok = cudaIpcOpenMemHandle((void**)&s.peer_flags[side], all[n].flags, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+            s.peer_is_ipc[side] = true;
         }
         cudaGetLastError();
     }
@@ -1012,6 +1082,34 @@ int heat3d_create(const heat3d_params* pin, heat3d_ctx** out)
         const bool want_ipc = !(ex && strcmp(ex, "nccl") == 0);
         if ((rc = setup_ipc(c, want_ipc))) { heat3d_destroy(c); return rc; }
     }
+    // slabs of this process reach each other by plain pointers (same device, or peer access enabled above)
+    bool reachable = true;
+    for (Slab& s : c->slabs)
+        for (int side = 0; side < 2; ++side) {
+            Slab* n = local_slab(c, s.gidx + (side == 0 ? -1 : 1));
+            if (!n) continue;
+            int can = 1;
+            if (n->dev != s.dev) cudaDeviceCanAccessPeer(&can, s.dev, n->dev);
+            reachable = reachable && can;
+            s.peer_buf[side][0] = n->buf[0];
+            s.peer_buf[side][1] = n->buf[1];
+            s.peer_flags[side] = n->d_flags;
+        }
+    {
+        // HEAT3D_EXCHANGE=store: the stencil kernel itself writes the outer planes into the neighbours' ghost planes
+        // (peer stores over NVLink) and publishes their arrival - no copy, no exchange stream.  Needs every neighbour's
+        // memory mapped here and slabs thick enough for two separate end chunks; otherwise the copy paths are used.
+        const char* ex = getenv("HEAT3D_EXCHANGE");
+        bool ok = ex && strcmp(ex, "store") == 0 && p.nslabs > 1 && c->end_signal && c->use_tma && !(p.flags & HEAT3D_FLAG_NO_OVERLAP) &&
+                  reachable && (!multi_process || c->slabs[0].ipc);
+        for (int g = 0; g < p.nslabs && ok; ++g) {      // same verdict on every process: look at all slabs, not just mine
+            long long a = (long long)((uint64_t)g * p.nz / p.nslabs), b = (long long)((uint64_t)(g + 1) * p.nz / p.nslabs);
+            if (a < 1) a = 1;
+            if (b > (long long)p.nz - 1) b = (long long)p.nz - 1;
+            ok = b - a >= 2 * p.temporal_k;
+        }
+        c->store_mode = ok;
+    }
     cudaSetDevice(c->slabs[0].dev);
     *out = c;
     return HEAT3D_OK;
@@ -1068,6 +1166,7 @@ const char* heat3d_kernel_name(const heat3d_ctx* c)
 const char* heat3d_exchange_name(const heat3d_ctx* c)
 {
     if (!c) return "";
+    if (c->store_mode) return "peer-store";
     if (c->multi_process) return c->slabs[0].ipc ? "ipc-put" : "nccl";
     return c->slabs.size() > 1 ? "peer-copy" : "none";
 }

@@ -250,7 +250,17 @@ struct TmaWork {
     int end_za[2], end_zb[2];     // their output plane ranges
     int mid_za, mid_zb;           // the rest, cut into chunks of chunk_len
     int chunk_len;
-    unsigned long long* done;     // nullptr when nobody listens
+    unsigned long long* done;     // copy-engine exchange: bumped once per finished end-chunk CTA; nullptr when nobody listens
+    // Peer-store exchange (optional): end chunk i also writes the planes [mirror_z0[i], mirror_z1[i]) it produces straight
+    // into the neighbouring slab's ghost planes (mirror[i] = the address local plane mirror_z0[i], row 0, column 0 maps
+    // to there: the neighbour's memory, reached over NVLink or on the same GPU), and the LAST CTA of that end chunk to
+    // finish (side_done[i] reaching side_goal[i]) publishes flag_value in the neighbour's arrival flag.
+    double* mirror[2];
+    int mirror_z0[2], mirror_z1[2];
+    unsigned long long* side_done[2];
+    unsigned long long side_goal[2];
+    unsigned long long* peer_flag[2];
+    unsigned long long flag_value;
 };
 
 __device__ __forceinline__ bool chunk_of_cta(const TmaWork& w, int cidx, int& zs, int& cnt)
@@ -266,11 +276,32 @@ __device__ __forceinline__ bool chunk_of_cta(const TmaWork& w, int cidx, int& zs
     return is_end;
 }
 
-__device__ __forceinline__ void signal_end_chunk(const TmaWork& w)
+// End-chunk CTA epilogue: make this CTA's stores (local and peer) visible, then count it.
+__device__ __forceinline__ void signal_end_chunk(const TmaWork& w, int cidx)
 {
-    __threadfence();              // this thread's stores are visible device-wide ...
+    __threadfence_system();       // this thread's stores are visible, also to the peer GPU ...
     __syncthreads();              // ... for every thread of the CTA ...
-    if (threadIdx.x == 0) atomicAdd(w.done, 1ULL);   // ... before the CTA is counted
+    if (threadIdx.x == 0) {       // ... before the CTA is counted
+        if (w.done) atomicAdd(w.done, 1ULL);
+        unsigned long long* sd = cidx == 0 ? w.side_done[0] : w.side_done[1];
+        if (sd) {
+            const unsigned long long goal = cidx == 0 ? w.side_goal[0] : w.side_goal[1];
+            if (atomicAdd(sd, 1ULL) + 1ULL == goal) {      // last CTA of this end chunk: every mirrored plane has landed
+                __threadfence_system();
+                *(volatile unsigned long long*)(cidx == 0 ? w.peer_flag[0] : w.peer_flag[1]) = w.flag_value;
+            }
+        }
+    }
+}
+
+// This thread's address in the neighbour's ghost planes for the chunk's first output plane zs, or nullptr.
+__device__ __forceinline__ double* mirror_origin(const TmaWork& w, bool is_end, int cidx, int zs, long long plane, long long row_off)
+{
+    if (!is_end) return nullptr;
+    double* m = cidx == 0 ? w.mirror[0] : w.mirror[1];
+    if (!m) return nullptr;
+    const int mz0 = cidx == 0 ? w.mirror_z0[0] : w.mirror_z0[1];
+    return m + (long long)(zs - mz0) * plane + row_off;
 }
 
 // Per-thread store plan, fixed for the whole chunk: which of the thread's cells exist and are interior.
@@ -280,11 +311,41 @@ struct StorePlan {
     uint32_t rows;     // bit r: row r is interior
 };
 
+// Residual contribution of one finished pair (only cells that are actually stored count).
+__device__ __forceinline__ void res_pair(double& rmax, const double2& o, const double2& c, const StorePlan& sp, int r)
+{
+    if (sp.all) {
+        res_track(rmax, o.x, c.x);
+        res_track(rmax, o.y, c.y);
+    } else if ((sp.rows >> r) & 1u) {
+        if (sp.x0) res_track(rmax, o.x, c.x);
+        if (sp.x1) res_track(rmax, o.y, c.y);
+    }
+}
+
+// Store one finished pair according to the thread's plan; `m` (nullptr = off) is the same cell in a neighbour's ghost plane.
+__device__ __forceinline__ void store_pair(double* __restrict__ o_ptr, double* __restrict__ m, const double2& o, const StorePlan& sp, int r)
+{
+    if (sp.all) {
+        *(double2*)o_ptr = o;
+        if (m) *(double2*)m = o;
+    } else if ((sp.rows >> r) & 1u) {
+        if (sp.x0) {
+            o_ptr[0] = o.x;
+            if (m) m[0] = o.x;
+        }
+        if (sp.x1) {
+            o_ptr[1] = o.y;
+            if (m) m[1] = o.y;
+        }
+    }
+}
+
 template <int RY, int ARITH, bool RES, bool FINISH>
 __device__ __forceinline__ void plane_update(const double* __restrict__ S, int row_pitch, double2 (&cn)[RY], const double2 (&cp1)[RY],
                                              const double2 (&cp2)[RY], double2 (&t)[RY], double2 (&tw)[RY],
-                                             double* __restrict__ out, int pitch, const StorePlan& sp, double Dx, double Dy,
-                                             double Dz, double& rmax)
+                                             double* __restrict__ out, double* __restrict__ mir, int pitch, const StorePlan& sp,
+                                             double Dx, double Dy, double Dz, double& rmax)
 {
     // one visit to the staged plane: own cells, x neighbours (left of .x, right of .y), y neighbours above/below the patch
     double xl[RY], xr[RY];
@@ -302,20 +363,8 @@ __device__ __forceinline__ void plane_update(const double* __restrict__ S, int r
             double2 o;
             o.x = finish_z2<ARITH>(t[r].x, tw[r].x, cp2[r].x, cn[r].x, Dz);
             o.y = finish_z2<ARITH>(t[r].y, tw[r].y, cp2[r].y, cn[r].y, Dz);
-            double* o_ptr = out + (long long)r * pitch;
-            if (sp.all) {
-                *(double2*)o_ptr = o;
-                if (RES) { res_track(rmax, o.x, cp1[r].x); res_track(rmax, o.y, cp1[r].y); }
-            } else if ((sp.rows >> r) & 1u) {
-                if (sp.x0) {
-                    o_ptr[0] = o.x;
-                    if (RES) res_track(rmax, o.x, cp1[r].x);
-                }
-                if (sp.x1) {
-                    o_ptr[1] = o.y;
-                    if (RES) res_track(rmax, o.y, cp1[r].y);
-                }
-            }
+            store_pair(out + (long long)r * pitch, mir ? mir + (long long)r * pitch : nullptr, o, sp, r);
+            if (RES) res_pair(rmax, o, cp1[r], sp, r);
         }
         const double2 ym = r == 0 ? up : cn[r - 1];
         const double2 yp = r == RY - 1 ? dn : cn[r + 1];
@@ -346,7 +395,8 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
     const int ntiles = w.ntx * w.nty;
     const int tile = blockIdx.x % ntiles;
     int zs, cnt;                                                // first output plane / number of output planes of this CTA
-    const bool is_end = chunk_of_cta(w, blockIdx.x / ntiles, zs, cnt);
+    const int cidx = blockIdx.x / ntiles;
+    const bool is_end = chunk_of_cta(w, cidx, zs, cnt);
     if (cnt <= 0) return;
     const int niter = cnt + 2;                                  // input planes zs-1 .. zs+cnt
     const int bx = (tile % w.ntx) * TX - 2;                     // TMA box origin
@@ -384,6 +434,11 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
         if (gy + r >= 1 && gy + r <= g.ny - 2) sp.rows |= 1u << r;
     sp.all = sp.x0 && sp.x1 && sp.rows == (1u << RY) - 1u;
     double* out = dst + (long long)zs * g.plane + (long long)gy * g.pitch + gx;
+    // peer-store exchange: where this thread's patch of output plane zs lives in the neighbour's ghost planes
+    double* mir = mirror_origin(w, is_end, cidx, zs, g.plane, (long long)gy * g.pitch + gx);
+    const int mz0 = cidx == 0 ? w.mirror_z0[0] : w.mirror_z0[1], mz1 = cidx == 0 ? w.mirror_z1[0] : w.mirror_z1[1];
+    int zout = zs;                                              // output plane the next finished plane goes to
+    auto mir_now = [&]() -> double* { return (mir && zout >= mz0 && zout < mz1) ? mir : nullptr; };
     const int soff = (1 + ry * RY) * ROW + 2 + 2 * lx;          // own first cell inside a stage
     double rmax = 0.0;
 
@@ -428,7 +483,7 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
     {
         const double* S = stage_ptr();
         mbar_wait(&full[s], ph);
-        plane_update<RY, ARITH, RES, false>(S, ROW, C[1], C[0], C[0], t, tw, out, g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
+        plane_update<RY, ARITH, RES, false>(S, ROW, C[1], C[0], C[0], t, tw, out, mir_now(), g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
         release_stage(1);
     }
     // q >= 2: plane p = zs-1+q arrives -> finish plane p-1 (index q-2 of the chunk) and form partial(p)
@@ -437,36 +492,44 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
         {
             const double* S = stage_ptr();
             mbar_wait(&full[s], ph);
-            plane_update<RY, ARITH, RES, true>(S, ROW, C[2], C[1], C[0], t, tw, out, g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
+            plane_update<RY, ARITH, RES, true>(S, ROW, C[2], C[1], C[0], t, tw, out, mir_now(), g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
             release_stage(q);
             out += g.plane;
+            if (mir) mir += g.plane;
+            ++zout;
         }
         {
             const double* S = stage_ptr();
             mbar_wait(&full[s], ph);
-            plane_update<RY, ARITH, RES, true>(S, ROW, C[0], C[2], C[1], t, tw, out, g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
+            plane_update<RY, ARITH, RES, true>(S, ROW, C[0], C[2], C[1], t, tw, out, mir_now(), g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
             release_stage(q + 1);
             out += g.plane;
+            if (mir) mir += g.plane;
+            ++zout;
         }
         {
             const double* S = stage_ptr();
             mbar_wait(&full[s], ph);
-            plane_update<RY, ARITH, RES, true>(S, ROW, C[1], C[0], C[2], t, tw, out, g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
+            plane_update<RY, ARITH, RES, true>(S, ROW, C[1], C[0], C[2], t, tw, out, mir_now(), g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
             release_stage(q + 2);
             out += g.plane;
+            if (mir) mir += g.plane;
+            ++zout;
         }
     }
     if (q < niter) {
         const double* S = stage_ptr();
         mbar_wait(&full[s], ph);
-        plane_update<RY, ARITH, RES, true>(S, ROW, C[2], C[1], C[0], t, tw, out, g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
+        plane_update<RY, ARITH, RES, true>(S, ROW, C[2], C[1], C[0], t, tw, out, mir_now(), g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
         release_stage(q);
         out += g.plane;
+        if (mir) mir += g.plane;
+        ++zout;
         ++q;
         if (q < niter) {
             const double* S2 = stage_ptr();
             mbar_wait(&full[s], ph);
-            plane_update<RY, ARITH, RES, true>(S2, ROW, C[0], C[2], C[1], t, tw, out, g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
+            plane_update<RY, ARITH, RES, true>(S2, ROW, C[0], C[2], C[1], t, tw, out, mir_now(), g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
             release_stage(q);
         }
     }
@@ -474,7 +537,7 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
         __syncthreads();                                      // every warp is done with the staged planes
         cta_residual_commit(rmax, res_slot, (unsigned long long*)smem);
     }
-    if (is_end && w.done) signal_end_chunk(w);
+    if (is_end && (w.done || w.side_done[0] || w.side_done[1])) signal_end_chunk(w, cidx);
 }
 
 // ------------------------------------------------------------------------------------------------------

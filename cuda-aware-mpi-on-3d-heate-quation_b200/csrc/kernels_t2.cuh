@@ -131,7 +131,8 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     const int ntiles = w.ntx * w.nty;
     const int tile = blockIdx.x % ntiles;
     int zs, cnt;                                                // first output (time n+2) plane / number of output planes
-    const bool is_end = chunk_of_cta(w, blockIdx.x / ntiles, zs, cnt);
+    const int cidx = blockIdx.x / ntiles;
+    const bool is_end = chunk_of_cta(w, cidx, zs, cnt);
     if (cnt <= 0) return;
     const int niter = cnt + 4;                                  // input planes zs-2 .. zs+cnt+1
     const int ox = (tile % w.ntx) * Cfg::OX, oy = (tile / w.ntx) * Cfg::OY;   // output tile origin
@@ -174,6 +175,10 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     pl.st.x1 = xin && pl.i1x1;
     pl.st.all = pl.st.x0 && pl.st.x1 && pl.st.rows == (1u << RY) - 1u;
     double* out = dst + (long long)zs * g.plane + (long long)gy * g.pitch + gx;
+    double* mir = mirror_origin(w, is_end, cidx, zs, g.plane, (long long)gy * g.pitch + gx);     // peer-store exchange
+    const int mz0 = cidx == 0 ? w.mirror_z0[0] : w.mirror_z0[1], mz1 = cidx == 0 ? w.mirror_z1[0] : w.mirror_z1[1];
+    int zout = zs;
+    auto mir_now = [&]() -> double* { return (mir && zout >= mz0 && zout < mz1) ? mir : nullptr; };
     const int soff = (1 + ry * RY) * ROW + 2 + 2 * lx;
     // SCHED 2 stores the mid plane split by x parity: a thread's left / right x neighbours are then 8-byte words at
     // consecutive lanes (2 wavefronts per warp load) instead of the second halves of 16-byte pairs (4 wavefronts).
@@ -236,24 +241,15 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
             if (q >= 4) level_step<RY, ARITH, true, true>(c1n, xl, xr, up, dn, c1p2, t1, tw1, o, g.Dx, g.Dy, g.Dz);
             else level_step<RY, ARITH, false, true>(c1n, xl, xr, up, dn, c1p2, t1, tw1, o, g.Dx, g.Dy, g.Dz);
             if (q >= 4) {
+                double* const mnow = mir_now();
 #pragma unroll
                 for (int r = 0; r < RY; ++r) {
-                    double* o_ptr = out + (long long)r * g.pitch;
-                    if (pl.st.all) {
-                        *(double2*)o_ptr = o[r];
-                        if (RES) { res_track(rmax, o[r].x, c1p1[r].x); res_track(rmax, o[r].y, c1p1[r].y); }
-                    } else if ((pl.st.rows >> r) & 1u) {
-                        if (pl.st.x0) {
-                            o_ptr[0] = o[r].x;
-                            if (RES) res_track(rmax, o[r].x, c1p1[r].x);
-                        }
-                        if (pl.st.x1) {
-                            o_ptr[1] = o[r].y;
-                            if (RES) res_track(rmax, o[r].y, c1p1[r].y);
-                        }
-                    }
+                    store_pair(out + (long long)r * g.pitch, mnow ? mnow + (long long)r * g.pitch : nullptr, o[r], pl.st, r);
+                    if (RES) res_pair(rmax, o[r], c1p1[r], pl.st, r);
                 }
                 out += g.plane;
+                if (mir) mir += g.plane;
+                ++zout;
             }
         }
         par ^= 1;
@@ -314,24 +310,15 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
             }
             double2 o[RY];
             level_full<RY, ARITH>(c1p1, xl, xr, up, dn, c1p2, c1n, o, g.Dx, g.Dy, g.Dz);
+            double* const mnow = mir_now();
 #pragma unroll
             for (int r = 0; r < RY; ++r) {
-                double* o_ptr = out + (long long)r * g.pitch;
-                if (pl.st.all) {
-                    *(double2*)o_ptr = o[r];
-                    if (RES) { res_track(rmax, o[r].x, c1p1[r].x); res_track(rmax, o[r].y, c1p1[r].y); }
-                } else if ((pl.st.rows >> r) & 1u) {
-                    if (pl.st.x0) {
-                        o_ptr[0] = o[r].x;
-                        if (RES) res_track(rmax, o[r].x, c1p1[r].x);
-                    }
-                    if (pl.st.x1) {
-                        o_ptr[1] = o[r].y;
-                        if (RES) res_track(rmax, o[r].y, c1p1[r].y);
-                    }
-                }
+                store_pair(out + (long long)r * g.pitch, mnow ? mnow + (long long)r * g.pitch : nullptr, o[r], pl.st, r);
+                if (RES) res_pair(rmax, o[r], c1p1[r], pl.st, r);
             }
             out += g.plane;
+            if (mir) mir += g.plane;
+            ++zout;
         }
         __syncthreads();        // plane q-1's stage has been read by everyone; this iteration's mid plane is complete
         if (q >= 1 && warp == (q & (NWARP - 1)) && lane == 0 && q - 1 + STAGES < niter) {
@@ -366,7 +353,7 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
         __syncthreads();
         cta_residual_commit(rmax, res_slot, (unsigned long long*)smem);
     }
-    if (is_end && w.done) signal_end_chunk(w);
+    if (is_end && (w.done || w.side_done[0] || w.side_done[1])) signal_end_chunk(w, cidx);
 }
 
 }  // namespace h3

@@ -206,7 +206,9 @@ const char* heat3d_kernel_name(const heat3d_ctx* ctx);
 
 /* How ghost planes travel in this context (static string): "none" (single slab), "peer-copy" (slabs of one process:
  * cudaMemcpyPeerAsync), "ipc-put" (other processes: copy-engine puts into CUDA-IPC-mapped ghost planes + stream-ordered
- * arrival flags; default) or "nccl" (ncclSend/ncclRecv; used when IPC is unavailable or HEAT3D_EXCHANGE=nccl is set). */
+ * arrival flags; default), "nccl" (ncclSend/ncclRecv; used when IPC is unavailable or HEAT3D_EXCHANGE=nccl is set) or
+ * "peer-store" (HEAT3D_EXCHANGE=store: the stencil kernel stores its outer planes directly into the neighbours' ghost
+ * planes and raises their arrival flags itself). */
 const char* heat3d_exchange_name(const heat3d_ctx* ctx);
 
 #ifdef __cplusplus

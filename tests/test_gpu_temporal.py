@@ -130,3 +130,45 @@ def test_depth2_large_grid_matches_depth1(h3):
         b.step(nsteps)
         B = b.download()
     assert np.array_equal(A, B)
+
+
+@pytest.mark.parametrize("k", [1, 2])
+@pytest.mark.parametrize("shape,P,nsteps", [((40, 24, 31), 2, 20), ((70, 40, 37), 3, 13), ((150, 70, 64), 4, 9), ((33, 17, 41), 8, 6)])
+def test_peer_store_exchange_bitwise(h3, oracle, k, shape, P, nsteps):
+    """HEAT3D_EXCHANGE=store: the stencil kernel writes its outer planes straight into the neighbouring slabs' ghost planes
+    and publishes the arrival flag itself (no copies, no exchange stream).  Same bar: bit-identical to the single domain,
+    also after an upload (copy-based ghost refresh) and across the speculative step of the convergence loop."""
+    nx, ny, nz = shape
+    os.environ["HEAT3D_EXCHANGE"] = "store"
+    try:
+        ref = _oracle_field(oracle, nx, ny, nz, nsteps)
+        prev = _oracle_field(oracle, nx, ny, nz, nsteps - 1)
+        with h3.Heat3D(nx, ny, nz, temporal_k=k, nslabs=P, devices=[0] * P, flags=h3.FLAG_TIME_HALO) as sim:
+            assert sim.exchange_name() == "peer-store"
+            sim.init_reference_field()
+            res = sim.step_residual(nsteps)
+            assert np.array_equal(sim.download(), ref)
+            assert res == oracle.residual(ref, prev)
+            T = np.random.default_rng(9).random((nz, ny, nx))
+            _, _, D = oracle.coefficients(nx, ny, nz)
+            sim.upload(T)
+            sim.step(7)
+            assert np.array_equal(sim.download(), oracle.steps(T.copy(), D, 7))
+            sim.init_reference_field()
+            applied, fin, conv = sim.run(11, 1e-30, check_every=1)
+            assert (applied, conv) == (11, False)
+            assert np.array_equal(sim.download(), _oracle_field(oracle, nx, ny, nz, 11))
+    finally:
+        os.environ.pop("HEAT3D_EXCHANGE", None)
+
+
+def test_peer_store_falls_back_on_thin_slabs(h3, oracle):
+    os.environ["HEAT3D_EXCHANGE"] = "store"
+    try:
+        with h3.Heat3D(21, 13, 12, temporal_k=2, nslabs=4, devices=[0] * 4) as sim:     # 3 planes per slab < 2 * ghost depth
+            assert sim.exchange_name() == "peer-copy"
+            sim.init_reference_field()
+            sim.step(6)
+            assert np.array_equal(sim.download(), _oracle_field(oracle, 21, 13, 12, 6))
+    finally:
+        os.environ.pop("HEAT3D_EXCHANGE", None)

@@ -134,7 +134,7 @@ struct TmaVariant {
     int tx, ty, ry, stages, minb;
     size_t smem;
     int threads;
-    const void* fn[2][2];   // [arith][res]
+    const void* fn[2][2][2];   // [arith][res][mirror]
 };
 
 template <int TX, int TY, int RY, int ST, int MINB>
@@ -145,10 +145,14 @@ TmaVariant make_variant(const char* name)
     v.tx = TX; v.ty = TY; v.ry = RY; v.stages = ST; v.minb = MINB;
     v.smem = h3::TmaCfg<TX, TY, ST>::SMEM_BYTES;
     v.threads = (TX / 2) * (TY / RY);
-    v.fn[0][0] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_STRICT, false, MINB>;
-    v.fn[0][1] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_STRICT, true, MINB>;
-    v.fn[1][0] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_FMA, false, MINB>;
-    v.fn[1][1] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_FMA, true, MINB>;
+    v.fn[0][0][0] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_STRICT, false, MINB, false>;
+    v.fn[0][1][0] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_STRICT, true, MINB, false>;
+    v.fn[1][0][0] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_FMA, false, MINB, false>;
+    v.fn[1][1][0] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_FMA, true, MINB, false>;
+    v.fn[0][0][1] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_STRICT, false, MINB, true>;
+    v.fn[0][1][1] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_STRICT, true, MINB, true>;
+    v.fn[1][0][1] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_FMA, false, MINB, true>;
+    v.fn[1][1][1] = (const void*)h3::stencil_tma_kernel<TX, TY, RY, ST, h3::ARITH_FMA, true, MINB, true>;
     return v;
 }
 
@@ -157,16 +161,10 @@ const std::vector<TmaVariant>& variants()
 {
     static const std::vector<TmaVariant> v = {
         make_variant<128, 8, 2, 4, 3>("tma_128x8_r2_s4_c3"),
-        make_variant<128, 8, 2, 5, 3>("tma_128x8_r2_s5_c3"),
         make_variant<128, 8, 4, 4, 4>("tma_128x8_r4_s4_c4"),
-        make_variant<128, 8, 4, 5, 4>("tma_128x8_r4_s5_c4"),
         make_variant<128, 16, 2, 4, 1>("tma_128x16_r2_s4_c1"),
         make_variant<128, 16, 4, 4, 2>("tma_128x16_r4_s4_c2"),
-        make_variant<128, 16, 4, 5, 2>("tma_128x16_r4_s5_c2"),
-        make_variant<128, 16, 8, 4, 2>("tma_128x16_r8_s4_c2"),
         make_variant<128, 32, 4, 4, 1>("tma_128x32_r4_s4_c1"),
-        make_variant<128, 32, 4, 5, 1>("tma_128x32_r4_s5_c1"),
-        make_variant<128, 32, 8, 5, 1>("tma_128x32_r8_s5_c1"),
         make_variant<64, 16, 4, 4, 4>("tma_64x16_r4_s4_c4"),
     };
     return v;
@@ -178,7 +176,7 @@ struct T2Variant {
     int cx, cy, ry, stages, minb, sched;
     size_t smem;
     int threads;
-    const void* fn[2][2];   // [arith][res]
+    const void* fn[2][2][2];   // [arith][res][mirror]
 };
 
 template <int CX, int CY, int RY, int ST, int MINB, int SCHED = 0>
@@ -189,10 +187,14 @@ T2Variant make_t2(const char* name)
     v.cx = CX; v.cy = CY; v.ry = RY; v.stages = ST; v.minb = MINB; v.sched = SCHED;
     v.smem = h3::Tma2Cfg<CX, CY, ST>::SMEM_BYTES;
     v.threads = (CX / 2) * (CY / RY);
-    v.fn[0][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, false, MINB, SCHED>;
-    v.fn[0][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, true, MINB, SCHED>;
-    v.fn[1][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, false, MINB, SCHED>;
-    v.fn[1][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, true, MINB, SCHED>;
+    v.fn[0][0][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, false, MINB, SCHED, false>;
+    v.fn[0][1][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, true, MINB, SCHED, false>;
+    v.fn[1][0][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, false, MINB, SCHED, false>;
+    v.fn[1][1][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, true, MINB, SCHED, false>;
+    v.fn[0][0][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, false, MINB, SCHED, true>;
+    v.fn[0][1][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, true, MINB, SCHED, true>;
+    v.fn[1][0][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, false, MINB, SCHED, true>;
+    v.fn[1][1][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, true, MINB, SCHED, true>;
     return v;
 }
 
@@ -205,19 +207,16 @@ const std::vector<T2Variant>& t2_variants()
         // 128 registers.  4 rows per thread = 12 % fewer shared-memory wavefronts per cell, the 64x32 region wastes
         // less on the redundant ring (60x30 of 64x32 useful): +4 % at 512^3, +8 % at 1024^2 planes (sustained).
         make_t2<64, 32, 4, 4, 2, 1>("t2_64x32_r4_s4_c2_L"),
-        make_t2<64, 32, 4, 4, 2, 2>("t2_64x32_r4_s4_c2_P"),
-        make_t2<64, 16, 4, 4, 3, 2>("t2_64x16_r4_s4_c3_P"),
         make_t2<64, 32, 4, 3, 2, 1>("t2_64x32_r4_s3_c2_L"),
         make_t2<64, 16, 4, 4, 3, 1>("t2_64x16_r4_s4_c3_L"),
-        make_t2<64, 16, 4, 5, 3, 1>("t2_64x16_r4_s5_c3_L"),
-        make_t2<64, 16, 4, 4, 4, 1>("t2_64x16_r4_s4_c4_L"),
         make_t2<64, 16, 2, 4, 3, 1>("t2_64x16_r2_s4_c3_L"),
+        // "_P" = schedule 2: schedule 1 with the mid plane split by x parity (no gain measured)
+        make_t2<64, 32, 4, 4, 2, 2>("t2_64x32_r4_s4_c2_P"),
         // schedule 0: partial_xy of the newest plane kept in registers (first version of the kernel)
         make_t2<64, 16, 2, 3, 2>("t2_64x16_r2_s3_c2"),
         make_t2<64, 16, 2, 4, 2>("t2_64x16_r2_s4_c2"),
         make_t2<64, 32, 2, 4, 1>("t2_64x32_r2_s4_c1"),
         make_t2<128, 16, 2, 4, 1>("t2_128x16_r2_s4_c1"),
-        make_t2<128, 8, 2, 4, 2>("t2_128x8_r2_s4_c2"),
     };
     return v;
 }
@@ -420,7 +419,7 @@ int launch_stencil(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res, in
         const long long grid = plan_chunks(w, za, zb, ends, /*end_len=*/8, c->p.tune[5] > 0 ? c->p.tune[5] : 16,
                                            (long long)s.num_sms * v.minb, s, mirrored ? &mi : nullptr);
         void* args[] = {(void*)&s.tmap[src], (void*)&dst, (void*)&g, (void*)&w, (void*)&s.d_res};
-        CU_TRY(cudaLaunchKernel(v.fn[ar][res ? 1 : 0], dim3((unsigned)grid), dim3(v.threads), args, v.smem, s.compute));
+        CU_TRY(cudaLaunchKernel(v.fn[ar][res ? 1 : 0][mirrored ? 1 : 0], dim3((unsigned)grid), dim3(v.threads), args, v.smem, s.compute));
     } else {
         const dim3 block(64, 4);
         const int nzp = zb - za;
@@ -463,7 +462,7 @@ int launch_stencil_t2(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res,
     const long long grid = plan_chunks(w, za, zb, ends, /*end_len=*/16, c->t2_chunk, (long long)s.num_sms * v.minb, s, mirrored ? &mi : nullptr);
     int z1lo = (int)(1 - s.zg0), z1hi = (int)((long long)c->p.nz - 1 - s.zg0);   // level-1 planes that are global interior planes
     void* args[] = {(void*)&s.tmap2[src], (void*)&dst, (void*)&g, (void*)&w, (void*)&z1lo, (void*)&z1hi, (void*)&s.d_res};
-    CU_TRY(cudaLaunchKernel(v.fn[ar][res ? 1 : 0], dim3((unsigned)grid), dim3(v.threads), args, v.smem, s.compute));
+    CU_TRY(cudaLaunchKernel(v.fn[ar][res ? 1 : 0][mirrored ? 1 : 0], dim3((unsigned)grid), dim3(v.threads), args, v.smem, s.compute));
     c->tm.launches++;
     c->tm.last_call_launches++;
     c->tm.last_call_stencil_launches++;
@@ -829,14 +828,16 @@ int setup_slab(heat3d_ctx* c, Slab& s)
             if ((rc = make_tmap(s, &s.tmap[w], w, c, v.tx + 4, v.ty + 2))) return rc;
         for (int ar = 0; ar < 2; ++ar)
             for (int r = 0; r < 2; ++r)
-                CU_TRY(cudaFuncSetAttribute(v.fn[ar][r], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v.smem));
+                for (int m = 0; m < 2; ++m)
+                    CU_TRY(cudaFuncSetAttribute(v.fn[ar][r][m], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v.smem));
         if (c->variant2) {
             const T2Variant& v2 = *c->variant2;
             for (int w = 0; w < 2; ++w)
                 if ((rc = make_tmap(s, &s.tmap2[w], w, c, v2.cx + 4, v2.cy + 2))) return rc;
             for (int ar = 0; ar < 2; ++ar)
                 for (int r = 0; r < 2; ++r)
-                    CU_TRY(cudaFuncSetAttribute(v2.fn[ar][r], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v2.smem));
+                    for (int m = 0; m < 2; ++m)
+                        CU_TRY(cudaFuncSetAttribute(v2.fn[ar][r][m], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)v2.smem));
         }
     }
     return HEAT3D_OK;

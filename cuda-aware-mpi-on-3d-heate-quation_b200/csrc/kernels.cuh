@@ -375,7 +375,9 @@ __device__ __forceinline__ void plane_update(const double* __restrict__ S, int r
     }
 }
 
-template <int TX, int TY, int RY, int STAGES, int ARITH, bool RES, int MINB>
+// MIRROR = peer-store exchange compiled in (end chunks also write into the neighbours' ghost planes); the plain
+// instantiation carries none of its registers or instructions.
+template <int TX, int TY, int RY, int STAGES, int ARITH, bool RES, int MINB, bool MIRROR>
 __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
     stencil_tma_kernel(const __grid_constant__ CUtensorMap tmap, double* __restrict__ dst, Geom g, TmaWork w,
                        unsigned long long* res_slot)
@@ -435,10 +437,10 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
     sp.all = sp.x0 && sp.x1 && sp.rows == (1u << RY) - 1u;
     double* out = dst + (long long)zs * g.plane + (long long)gy * g.pitch + gx;
     // peer-store exchange: where this thread's patch of output plane zs lives in the neighbour's ghost planes
-    double* mir = mirror_origin(w, is_end, cidx, zs, g.plane, (long long)gy * g.pitch + gx);
+    double* mir = MIRROR ? mirror_origin(w, is_end, cidx, zs, g.plane, (long long)gy * g.pitch + gx) : nullptr;
     const int mz0 = cidx == 0 ? w.mirror_z0[0] : w.mirror_z0[1], mz1 = cidx == 0 ? w.mirror_z1[0] : w.mirror_z1[1];
     int zout = zs;                                              // output plane the next finished plane goes to
-    auto mir_now = [&]() -> double* { return (mir && zout >= mz0 && zout < mz1) ? mir : nullptr; };
+    auto mir_now = [&]() -> double* { return (MIRROR && mir && zout >= mz0 && zout < mz1) ? mir : nullptr; };
     const int soff = (1 + ry * RY) * ROW + 2 + 2 * lx;          // own first cell inside a stage
     double rmax = 0.0;
 
@@ -495,8 +497,7 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
             plane_update<RY, ARITH, RES, true>(S, ROW, C[2], C[1], C[0], t, tw, out, mir_now(), g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
             release_stage(q);
             out += g.plane;
-            if (mir) mir += g.plane;
-            ++zout;
+            if (MIRROR) { if (mir) mir += g.plane; ++zout; }
         }
         {
             const double* S = stage_ptr();
@@ -504,8 +505,7 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
             plane_update<RY, ARITH, RES, true>(S, ROW, C[0], C[2], C[1], t, tw, out, mir_now(), g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
             release_stage(q + 1);
             out += g.plane;
-            if (mir) mir += g.plane;
-            ++zout;
+            if (MIRROR) { if (mir) mir += g.plane; ++zout; }
         }
         {
             const double* S = stage_ptr();
@@ -513,8 +513,7 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
             plane_update<RY, ARITH, RES, true>(S, ROW, C[1], C[0], C[2], t, tw, out, mir_now(), g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
             release_stage(q + 2);
             out += g.plane;
-            if (mir) mir += g.plane;
-            ++zout;
+            if (MIRROR) { if (mir) mir += g.plane; ++zout; }
         }
     }
     if (q < niter) {
@@ -523,8 +522,7 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
         plane_update<RY, ARITH, RES, true>(S, ROW, C[2], C[1], C[0], t, tw, out, mir_now(), g.pitch, sp, g.Dx, g.Dy, g.Dz, rmax);
         release_stage(q);
         out += g.plane;
-        if (mir) mir += g.plane;
-        ++zout;
+        if (MIRROR) { if (mir) mir += g.plane; ++zout; }
         ++q;
         if (q < niter) {
             const double* S2 = stage_ptr();
@@ -537,7 +535,7 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
         __syncthreads();                                      // every warp is done with the staged planes
         cta_residual_commit(rmax, res_slot, (unsigned long long*)smem);
     }
-    if (is_end && (w.done || w.side_done[0] || w.side_done[1])) signal_end_chunk(w, cidx);
+    if (is_end && (w.done || (MIRROR && (w.side_done[0] || w.side_done[1])))) signal_end_chunk(w, cidx);
 }
 
 // ------------------------------------------------------------------------------------------------------

@@ -107,7 +107,7 @@ __device__ __forceinline__ void load_neighbours(const double* __restrict__ S, in
 //          the whole update of plane p-1 is formed when plane p has arrived (level 1), likewise for level 2 from the
 //          previous mid plane.  Same arithmetic, ~32 fewer registers per thread.
 // SCHED 2: schedule 1 with the mid plane stored split by x parity (cheaper x-neighbour loads at level 2).
-template <int CX, int CY, int RY, int STAGES, int ARITH, bool RES, int MINB, int SCHED>
+template <int CX, int CY, int RY, int STAGES, int ARITH, bool RES, int MINB, int SCHED, bool MIRROR>
 __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     stencil_tma_t2_kernel(const __grid_constant__ CUtensorMap tmap, double* __restrict__ dst, Geom g, TmaWork w, int z1lo, int z1hi,
                           unsigned long long* res_slot)
@@ -175,10 +175,10 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     pl.st.x1 = xin && pl.i1x1;
     pl.st.all = pl.st.x0 && pl.st.x1 && pl.st.rows == (1u << RY) - 1u;
     double* out = dst + (long long)zs * g.plane + (long long)gy * g.pitch + gx;
-    double* mir = mirror_origin(w, is_end, cidx, zs, g.plane, (long long)gy * g.pitch + gx);     // peer-store exchange
+    double* mir = MIRROR ? mirror_origin(w, is_end, cidx, zs, g.plane, (long long)gy * g.pitch + gx) : nullptr;     // peer-store exchange
     const int mz0 = cidx == 0 ? w.mirror_z0[0] : w.mirror_z0[1], mz1 = cidx == 0 ? w.mirror_z1[0] : w.mirror_z1[1];
     int zout = zs;
-    auto mir_now = [&]() -> double* { return (mir && zout >= mz0 && zout < mz1) ? mir : nullptr; };
+    auto mir_now = [&]() -> double* { return (MIRROR && mir && zout >= mz0 && zout < mz1) ? mir : nullptr; };
     const int soff = (1 + ry * RY) * ROW + 2 + 2 * lx;
     // SCHED 2 stores the mid plane split by x parity: a thread's left / right x neighbours are then 8-byte words at
     // consecutive lanes (2 wavefronts per warp load) instead of the second halves of 16-byte pairs (4 wavefronts).
@@ -248,8 +248,7 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
                     if (RES) res_pair(rmax, o[r], c1p1[r], pl.st, r);
                 }
                 out += g.plane;
-                if (mir) mir += g.plane;
-                ++zout;
+                if (MIRROR) { if (mir) mir += g.plane; ++zout; }
             }
         }
         par ^= 1;
@@ -317,8 +316,7 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
                 if (RES) res_pair(rmax, o[r], c1p1[r], pl.st, r);
             }
             out += g.plane;
-            if (mir) mir += g.plane;
-            ++zout;
+            if (MIRROR) { if (mir) mir += g.plane; ++zout; }
         }
         __syncthreads();        // plane q-1's stage has been read by everyone; this iteration's mid plane is complete
         if (q >= 1 && warp == (q & (NWARP - 1)) && lane == 0 && q - 1 + STAGES < niter) {
@@ -353,7 +351,7 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
         __syncthreads();
         cta_residual_commit(rmax, res_slot, (unsigned long long*)smem);
     }
-    if (is_end && (w.done || w.side_done[0] || w.side_done[1])) signal_end_chunk(w, cidx);
+    if (is_end && (w.done || (MIRROR && (w.side_done[0] || w.side_done[1])))) signal_end_chunk(w, cidx);
 }
 
 }  // namespace h3

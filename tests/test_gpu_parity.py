@@ -16,8 +16,7 @@ def h3():
 
 
 KERNELS = [("baseline", dict(kernel=1)), ("tma", dict(kernel=2))]
-TUNES = [(128, 8, 2, 4, 3), (128, 8, 2, 5, 3), (128, 8, 4, 4, 4), (128, 8, 4, 5, 4), (128, 16, 2, 4, 1), (128, 16, 4, 4, 2),
-         (128, 16, 4, 5, 2), (128, 16, 8, 4, 2), (128, 32, 4, 4, 1), (128, 32, 4, 5, 1), (128, 32, 8, 5, 1), (64, 16, 4, 4, 4)]
+TUNES = [(128, 8, 2, 4, 3), (128, 8, 4, 4, 4), (128, 16, 2, 4, 1), (128, 16, 4, 4, 2), (128, 32, 4, 4, 1), (64, 16, 4, 4, 4)]
 
 
 def _oracle_field(oracle, nx, ny, nz, nsteps, arith=0):

@@ -10,8 +10,8 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 # cx,cy,rows/thread,stages,CTAs/SM[,chunk_len,schedule]
-T2_TUNES = ["64,32,4,4,2,7,2", "64,16,4,4,3,7,2", "64,32,4,4,2,7,1", "64,32,4,3,2,7,1", "64,16,4,4,3,7,1", "64,16,4,5,3,7,1", "64,16,4,4,4,7,1", "64,16,2,4,3,7,1",
-            "64,16,2,3,2", "64,16,2,4,2", "64,32,2,4,1", "128,16,2,4,1", "128,8,2,4,2"]
+T2_TUNES = ["64,32,4,4,2,7,1", "64,32,4,3,2,7,1", "64,16,4,4,3,7,1", "64,16,2,4,3,7,1", "64,32,4,4,2,7,2",
+            "64,16,2,3,2", "64,16,2,4,2", "64,32,2,4,1", "128,16,2,4,1"]
 
 
 @pytest.fixture(scope="module")

@@ -18,8 +18,7 @@ try:
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
 except Exception:
     pass
-TUNES = [(128, 8, 2, 4, 3), (128, 8, 2, 5, 3), (128, 8, 4, 4, 4), (128, 8, 4, 5, 4), (128, 16, 2, 4, 1), (128, 16, 4, 4, 2),
-         (128, 16, 4, 5, 2), (128, 16, 8, 4, 2), (128, 32, 4, 4, 1), (128, 32, 4, 5, 1), (128, 32, 8, 5, 1), (64, 16, 4, 4, 4)]
+TUNES = [(128, 8, 2, 4, 3), (128, 8, 4, 4, 4), (128, 16, 2, 4, 1), (128, 16, 4, 4, 2), (128, 32, 4, 4, 1), (64, 16, 4, 4, 4)]
 cells = (n - 2) ** 3
 rows = []
 extra = [dict(kernel=2, tune=t + (c,)) for t in [(128, 8, 2, 4, 3), (128, 8, 4, 4, 4), (128, 16, 4, 4, 2)] for c in (12, 24)]

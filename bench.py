@@ -169,6 +169,15 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not os.path.exists(h3.LIB_PATH):
+        # not built yet (fresh checkout): compile the native library once - there is nothing else this could run on
+        if rank == 0:
+            ge.build()
+        else:
+            for _ in range(900):
+                if os.path.exists(h3.LIB_PATH):
+                    break
+                time.sleep(1.0)
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (the product has no CPU path); use --impl reference for the CPU baseline")
     torch.cuda.set_device(local)

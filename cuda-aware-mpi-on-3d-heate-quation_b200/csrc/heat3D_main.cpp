@@ -12,7 +12,8 @@
 //   HEAT3D_ARITH=strict|fma   arithmetic order of the update (default strict = the host program's)
 //   HEAT3D_CHECK_EVERY=N   examine the residual every N iterations (default 1 = reference semantics)
 //   HEAT3D_OUT_EVERY=M     also write output/out_<iteration>.dat every M iterations (async snapshots)
-//   HEAT3D_TEMPORAL_K=1|2  updates fused per HBM pass (bit-identical results; 2 pays off once CHECK_EVERY >= 2)
+//   HEAT3D_TEMPORAL_K=1|2  updates fused per HBM pass (bit-identical results either way).  Default: 2 for grids of
+//                          2^25 points and more, where a pass is long against a host round trip, else 1
 //   HEAT3D_KERNEL=auto|tma|baseline
 //   HEAT3D_PERF=1          print GLUPS / algorithmic GB/s to stderr
 #include "../../include/heat3d.h"
@@ -142,7 +143,9 @@ int main(int argc, char** argv)
     p.arith = (arithEnv && std::string(arithEnv) == "fma") ? HEAT3D_ARITH_FMA : HEAT3D_ARITH_STRICT;
     if (kernEnv && std::string(kernEnv) == "baseline") p.kernel = HEAT3D_KERNEL_BASELINE;
     if (kernEnv && std::string(kernEnv) == "tma") p.kernel = HEAT3D_KERNEL_TMA;
-    p.temporal_k = (int32_t)std::max(1u, env_unsigned("HEAT3D_TEMPORAL_K", 1));
+    const size_t points = (size_t)numCells[0] * numCells[1] * numCells[2];
+    p.temporal_k = (int32_t)std::max(1u, env_unsigned("HEAT3D_TEMPORAL_K", points >= ((size_t)1 << 25) ? 2u : 1u));
+    if (p.kernel == HEAT3D_KERNEL_BASELINE) p.temporal_k = 1;
     std::vector<int32_t> devices(ndev);
     for (unsigned i = 0; i < ndev; ++i) devices[i] = (int32_t)i;
     p.nslabs = (int32_t)ndev; p.slab_first = 0; p.nlocal = (int32_t)ndev;

@@ -461,7 +461,8 @@ int launch_stencil_t2(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res,
     const bool mirrored = fill_mirror(c, s, src ^ 1, ends, mi);
     const long long grid = plan_chunks(w, za, zb, ends, /*end_len=*/16, c->t2_chunk, (long long)s.num_sms * v.minb, s, mirrored ? &mi : nullptr);
     int z1lo = (int)(1 - s.zg0), z1hi = (int)((long long)c->p.nz - 1 - s.zg0);   // level-1 planes that are global interior planes
-    void* args[] = {(void*)&s.tmap2[src], (void*)&dst, (void*)&g, (void*)&w, (void*)&z1lo, (void*)&z1hi, (void*)&s.d_res};
+    unsigned long long* first = res ? s.d_res_base + 2 : nullptr;     // residual of the first of the two updates
+    void* args[] = {(void*)&s.tmap2[src], (void*)&dst, (void*)&g, (void*)&w, (void*)&z1lo, (void*)&z1hi, (void*)&s.d_res, (void*)&first};
     CU_TRY(cudaLaunchKernel(v.fn[ar][res ? 1 : 0][mirrored ? 1 : 0], dim3((unsigned)grid), dim3(v.threads), args, v.smem, s.compute));
     c->tm.launches++;
     c->tm.last_call_launches++;
@@ -598,6 +599,7 @@ int step_block(heat3d_ctx* c, int k, bool res)
         if (rc) return rc;
         if (c->snap_buf == dst) CU_TRY(cudaStreamWaitEvent(s.compute, s.ev_snap, 0));
         if (res && !c->res_slot_prezeroed) CU_TRY(cudaMemsetAsync(s.d_res, 0, sizeof(unsigned long long), s.compute));
+        if (res && k == 2) CU_TRY(cudaMemsetAsync(s.d_res_base + 2, 0, sizeof(unsigned long long), s.compute));
         if (!s.lower && !s.upper) {
             if ((rc = launch(s, src, s.za, s.zb, res, 0))) return rc;
             continue;
@@ -798,7 +800,7 @@ int setup_slab(heat3d_ctx* c, Slab& s)
             CU_TRY(cudaEventCreate(&s.ev_wait1[i]));
         }
     }
-    CU_TRY(cudaMalloc(&s.d_res_base, 2 * sizeof(unsigned long long)));
+    CU_TRY(cudaMalloc(&s.d_res_base, 3 * sizeof(unsigned long long)));   // [0],[1]: slots of the depth-1 loop; [2]: first update of a depth-2 pass
     s.d_res = s.d_res_base;
     for (cudaEvent_t& e : s.ev_res) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     CU_TRY(cudaMalloc(&s.d_done, sizeof(unsigned long long)));
@@ -807,7 +809,7 @@ int setup_slab(heat3d_ctx* c, Slab& s)
     CU_TRY(cudaMemset(s.d_side_done, 0, 2 * sizeof(unsigned long long)));
     CU_TRY(cudaMalloc(&s.d_flags, 2 * sizeof(unsigned long long)));
     CU_TRY(cudaMemset(s.d_flags, 0, 2 * sizeof(unsigned long long)));
-    CU_TRY(cudaMemset(s.d_res_base, 0, 2 * sizeof(unsigned long long)));
+    CU_TRY(cudaMemset(s.d_res_base, 0, 3 * sizeof(unsigned long long)));
     s.partial_blocks = s.num_sms * 8;
     CU_TRY(cudaMalloc(&s.d_partial, (size_t)s.partial_blocks * sizeof(double)));
     CU_TRY(cudaMalloc(&s.d_scalar, 2 * sizeof(double)));
@@ -1438,6 +1440,66 @@ static int run_every_iteration(heat3d_ctx* c, uint32_t iter_max, double eps, uin
     return end_call(c);
 }
 
+// The same loop on a depth-2 context: one pass advances two iterations and its kernel reports BOTH residuals, so the
+// reference's every-iteration check costs one host round trip per two iterations.  No speculation here (the next pass
+// would overwrite the buffer a rollback needs): if the FIRST of the two iterations is the converging one, the pass is
+// undone by flipping `cur` back and that single iteration is redone with the depth-1 kernel.
+static int run_every_iteration_t2(heat3d_ctx* c, uint32_t iter_max, double eps, uint32_t* fin, int32_t* conv, uint32_t* done)
+{
+    int rc = begin_call(c);
+    if (rc) return rc;
+    double norm = 1.0;                                       // cu:325
+    auto read_pair = [&](double& first, double& second) -> int {
+        first = second = 0.0;
+        for (Slab& s : c->slabs) {
+            int r0 = set_dev(s);
+            if (r0) return r0;
+            CU_TRY(cudaMemcpyAsync(s.h_scalar + 2, s.d_res_base, sizeof(double), cudaMemcpyDeviceToHost, s.compute));
+            CU_TRY(cudaMemcpyAsync(s.h_scalar + 3, s.d_res_base + 2, sizeof(double), cudaMemcpyDeviceToHost, s.compute));
+            CU_TRY(cudaStreamSynchronize(s.compute));
+            if (s.h_scalar[2] > second) second = s.h_scalar[2];
+            if (s.h_scalar[3] > first) first = s.h_scalar[3];
+        }
+        if (first < DBL_MIN) first = DBL_MIN;                // cu:1019
+        if (second < DBL_MIN) second = DBL_MIN;
+        return HEAT3D_OK;
+    };
+    uint32_t time = 0;
+    while (time < iter_max) {
+        double r1 = 0.0, r2 = 0.0;
+        if (time + 1 < iter_max) {
+            if ((rc = step_block(c, 2, true))) return rc;
+            if ((rc = read_pair(r1, r2))) return rc;
+            ++*done;
+            if (time == 0 && r1 != 0.0) norm = r1;           // cu:1030-1032
+            if (r1 / norm < eps) {                           // iteration `time` converged: keep only that one update
+                if ((rc = heat3d_sync(c))) return rc;
+                c->cur ^= 1;
+                c->tm.steps -= 2;
+                if ((rc = step_block(c, 1, true))) return rc;
+                double single = 0.0;
+                if ((rc = fetch_residual(c, &single))) return rc;
+                *conv = 1;
+                *fin = time;
+                break;
+            }
+            ++*done;
+            c->have_res = true;
+            c->last_res = r2;
+            if (r2 / norm < eps) { *conv = 1; *fin = time + 1; break; }     // cu:1055-1073
+            time += 2;
+        } else {
+            if ((rc = step_block(c, 1, true))) return rc;
+            if ((rc = fetch_residual(c, &r1))) return rc;
+            ++*done;
+            if (time == 0 && r1 != 0.0) norm = r1;
+            if (r1 / norm < eps) { *conv = 1; *fin = time; }
+            break;
+        }
+    }
+    return end_call(c);
+}
+
 int heat3d_run(heat3d_ctx* c, uint32_t iter_max, double eps, uint32_t check_every, uint32_t* final_iters, int32_t* converged,
                uint32_t* applied)
 {
@@ -1449,7 +1511,8 @@ int heat3d_run(heat3d_ctx* c, uint32_t iter_max, double eps, uint32_t check_ever
     int32_t conv = 0;
     uint32_t time = 0;
     if (check_every == 1 && !c->multi_process && c->snap_buf < 0) {
-        if ((rc = run_every_iteration(c, iter_max, eps, &fin, &conv, &done))) return rc;
+        if ((rc = c->variant2 ? run_every_iteration_t2(c, iter_max, eps, &fin, &conv, &done)
+                              : run_every_iteration(c, iter_max, eps, &fin, &conv, &done))) return rc;
         time = iter_max;
     }
     while (time < iter_max) {

@@ -110,7 +110,7 @@ __device__ __forceinline__ void load_neighbours(const double* __restrict__ S, in
 template <int CX, int CY, int RY, int STAGES, int ARITH, bool RES, int MINB, int SCHED, bool MIRROR>
 __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     stencil_tma_t2_kernel(const __grid_constant__ CUtensorMap tmap, double* __restrict__ dst, Geom g, TmaWork w, int z1lo, int z1hi,
-                          unsigned long long* res_slot)
+                          unsigned long long* res_slot, unsigned long long* res_slot_first)
 {
     using Cfg = Tma2Cfg<CX, CY, STAGES>;
     constexpr int NTHR = (CX / 2) * (CY / RY);
@@ -186,7 +186,9 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     constexpr int MHALF = (CY + 2) * MP;                 // one parity array; two of them fit one STAGE_STRIDE
     static_assert(2 * MHALF * 8 <= Cfg::STAGE_STRIDE, "split mid plane must fit the mid buffer");
     const int moff = (1 + ry * RY) * MP + 1 + lx;
-    double rmax = 0.0;
+    double rmax = 0.0;      // residual of the second update (time n+1 -> n+2), over the cells this CTA stores
+    double rmax1 = 0.0;     // residual of the first update (time n -> n+1), over every level-1 cell this CTA forms: cells
+                            // shared with neighbouring CTAs are counted more than once, which a maximum does not mind
 
     double2 C0[3][RY], t0[RY], tw0[RY];      // level 0: centres of the last three planes, partial / 2*centre of the newest
     double2 C1[3][RY], t1[RY], tw1[RY];      // level 1: same
@@ -220,6 +222,13 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
                     const bool row = zint && ((pl.rows1 >> r) & 1u);
                     if (!(row && pl.i1x0)) c1n[r].x = c0p1[r].x;
                     if (!(row && pl.i1x1)) c1n[r].y = c0p1[r].y;
+                }
+            }
+            if (RES) {
+#pragma unroll
+                for (int r = 0; r < RY; ++r) {
+                    res_track(rmax1, c1n[r].x, c0p1[r].x);
+                    res_track(rmax1, c1n[r].y, c0p1[r].y);
                 }
             }
             double* M = (double*)(mid + par * Cfg::STAGE_STRIDE) + soff;
@@ -276,6 +285,13 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
                     const bool row = zint && ((pl.rows1 >> r) & 1u);
                     if (!(row && pl.i1x0)) c1n[r].x = c0p1[r].x;
                     if (!(row && pl.i1x1)) c1n[r].y = c0p1[r].y;
+                }
+            }
+            if (RES) {
+#pragma unroll
+                for (int r = 0; r < RY; ++r) {
+                    res_track(rmax1, c1n[r].x, c0p1[r].x);
+                    res_track(rmax1, c1n[r].y, c0p1[r].y);
                 }
             }
             if (SCHED == 2) {   // even-x cells and odd-x cells in separate arrays (see MP below)
@@ -350,6 +366,10 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     if (RES) {
         __syncthreads();
         cta_residual_commit(rmax, res_slot, (unsigned long long*)smem);
+        if (res_slot_first) {
+            __syncthreads();
+            cta_residual_commit(rmax1, res_slot_first, (unsigned long long*)smem);
+        }
     }
     if (is_end && (w.done || (MIRROR && (w.side_done[0] || w.side_done[1])))) signal_end_chunk(w, cidx);
 }

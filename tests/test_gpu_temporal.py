@@ -172,3 +172,38 @@ def test_peer_store_falls_back_on_thin_slabs(h3, oracle):
             assert np.array_equal(sim.download(), _oracle_field(oracle, 21, 13, 12, 6))
     finally:
         os.environ.pop("HEAT3D_EXCHANGE", None)
+
+
+@pytest.mark.parametrize("P", [1, 3])
+def test_depth2_every_iteration_convergence_loop_is_exact(h3, oracle, P):
+    """check_every=1 on a depth-2 context: each pass reports the residuals of BOTH its updates.  Iteration counts and
+    fields must be the reference's whether the converging iteration is the first or the second of a pass."""
+    nx = ny = nz = 27
+    _, _, D = oracle.coefficients(nx, ny, nz)
+    parities = set()
+    for eps, iter_max in ((1e-6, 100000), (2e-6, 100000), (3e-6, 100000), (5e-6, 100000), (1e-30, 37), (1e-30, 40)):
+        T = oracle.init_field(nx, ny, nz)
+        applied_o, fin_o, conv_o = oracle.run(T, D, iter_max, eps)
+        if conv_o:
+            parities.add(fin_o % 2)
+        with h3.Heat3D(nx, ny, nz, temporal_k=2, nslabs=P, devices=[0] * P) as sim:
+            sim.init_reference_field()
+            assert sim.run(iter_max, eps, check_every=1) == (applied_o, fin_o, conv_o)
+            assert sim.timing()["steps"] == applied_o
+            assert np.array_equal(sim.download(), T)
+            sim.step(3)
+            assert np.array_equal(sim.download(), oracle.steps(T.copy(), D, 3))
+    assert parities == {0, 1}, parities          # both kinds of ending were exercised
+
+
+def test_depth2_first_update_residual_matches_oracle(h3, oracle):
+    nx, ny, nz = 70, 37, 45
+    _, _, D = oracle.coefficients(nx, ny, nz)
+    a = oracle.steps(oracle.init_field(nx, ny, nz), D, 8)
+    b = oracle.steps(a.copy(), D, 1)
+    c2 = oracle.steps(b.copy(), D, 1)
+    with h3.Heat3D(nx, ny, nz, temporal_k=2, nslabs=2, devices=[0, 0]) as sim:
+        sim.init_reference_field()
+        sim.step(8)
+        assert sim.step_residual(2) == oracle.residual(c2, b)       # the second update's residual is what this call returns
+        assert np.array_equal(sim.download(), c2)

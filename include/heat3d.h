@@ -57,7 +57,7 @@ typedef enum heat3d_status {
  *         host program;  FMA: the contraction nvcc emits for the reference kernel (3 fused multiply-adds). */
 enum { HEAT3D_ARITH_STRICT = 0, HEAT3D_ARITH_FMA = 1 };
 
-/* Stencil kernel selection.  AUTO picks the TMA-staged z-streaming kernel. */
+/* Stencil kernel selection.  AUTO picks the TMA-staged z-streaming kernels (depth 1, and depth 2 when temporal_k = 2). */
 enum { HEAT3D_KERNEL_AUTO = 0, HEAT3D_KERNEL_BASELINE = 1, HEAT3D_KERNEL_TMA = 2 };
 
 typedef struct heat3d_ctx heat3d_ctx;
@@ -67,7 +67,8 @@ typedef struct heat3d_params {
     uint32_t nx, ny, nz;        /* global point counts (cu:332-335), each >= 3                             */
     double Dx, Dy, Dz;          /* dt*alpha/sp^2 as the caller derives them (cu:359-367)                  */
     int32_t arith;              /* HEAT3D_ARITH_*                                                          */
-    int32_t temporal_k;         /* time steps fused per HBM pass = ghost depth; 0/1 = none                 */
+    int32_t temporal_k;         /* FTCS updates fused per HBM pass = ghost depth: 1 (0 means 1) or 2; results are
+                                   bit-identical either way                                                */
     int32_t kernel;             /* HEAT3D_KERNEL_*                                                         */
     int32_t nslabs;             /* total z-slabs over all processes; 0/1 = single slab                     */
     int32_t slab_first;         /* first slab owned by this context                                        */
@@ -144,10 +145,13 @@ int heat3d_step(heat3d_ctx* ctx, uint32_t nsteps);
 int heat3d_step_residual(heat3d_ctx* ctx, uint32_t nsteps, double* residual);
 
 /* The reference's time loop (cu:541-1074): iterate until res/norm < eps or iter_max; norm = residual of
- * iteration 0 (cu:1030-1032).  The residual is examined on iterations 0, and every `check_every`-th
- * thereafter (check_every = 1 reproduces the reference's iteration count exactly).  *final_iters receives
- * the reference's finalNumIterations (0-based index of the converging iteration, cu:1070-1073; 0 if not
- * converged), *converged its globalBreakCondition, *applied (optional) the number of updates performed. */
+ * iteration 0 (cu:1030-1032).  The residual is examined on iteration 0 and every `check_every`-th thereafter
+ * (check_every = 1 reproduces the reference's iteration count exactly, and the field is then the state after
+ * exactly that iteration).  With check_every = 1 the GPU is not left waiting for the host's check: on a depth-1
+ * context the next iteration is queued ahead and dropped again if it turns out not to be needed; on a depth-2
+ * context one pass yields the residuals of both its iterations.  *final_iters receives the reference's
+ * finalNumIterations (0-based index of the converging iteration, cu:1070-1073; 0 if not converged), *converged its
+ * globalBreakCondition, *applied (optional) the number of updates performed. */
 int heat3d_run(heat3d_ctx* ctx, uint32_t iter_max, double eps, uint32_t check_every,
                uint32_t* final_iters, int32_t* converged, uint32_t* applied);
 

@@ -9,12 +9,14 @@
 #include "internal.h"
 
 #include <algorithm>
+#include <array>
 #include <cfloat>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <dlfcn.h>
+#include <map>
 #include <new>
 #include <vector>
 
@@ -173,50 +175,47 @@ const std::vector<TmaVariant>& variants()
 // ---- depth-2 temporal-blocking kernel variants --------------------------------------------------------
 struct T2Variant {
     const char* name;
-    int cx, cy, ry, stages, minb, sched;
+    int cx, cy, ry, stages, minb, xmode;
     size_t smem;
     int threads;
     const void* fn[2][2][2];   // [arith][res][mirror]
 };
 
-template <int CX, int CY, int RY, int ST, int MINB, int SCHED = 0>
+template <int CX, int CY, int RY, int ST, int MINB, int XSW>
 T2Variant make_t2(const char* name)
 {
     T2Variant v;
     v.name = name;
-    v.cx = CX; v.cy = CY; v.ry = RY; v.stages = ST; v.minb = MINB; v.sched = SCHED;
+    v.cx = CX; v.cy = CY; v.ry = RY; v.stages = ST; v.minb = MINB; v.xmode = XSW;
     v.smem = h3::Tma2Cfg<CX, CY, ST>::SMEM_BYTES;
     v.threads = (CX / 2) * (CY / RY);
-    v.fn[0][0][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, false, MINB, SCHED, false>;
-    v.fn[0][1][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, true, MINB, SCHED, false>;
-    v.fn[1][0][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, false, MINB, SCHED, false>;
-    v.fn[1][1][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, true, MINB, SCHED, false>;
-    v.fn[0][0][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, false, MINB, SCHED, true>;
-    v.fn[0][1][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, true, MINB, SCHED, true>;
-    v.fn[1][0][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, false, MINB, SCHED, true>;
-    v.fn[1][1][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, true, MINB, SCHED, true>;
+    v.fn[0][0][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, false, MINB, XSW, false>;
+    v.fn[0][1][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, true, MINB, XSW, false>;
+    v.fn[1][0][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, false, MINB, XSW, false>;
+    v.fn[1][1][0] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, true, MINB, XSW, false>;
+    v.fn[0][0][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, false, MINB, XSW, true>;
+    v.fn[0][1][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_STRICT, true, MINB, XSW, true>;
+    v.fn[1][0][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, false, MINB, XSW, true>;
+    v.fn[1][1][1] = (const void*)h3::stencil_tma_t2_kernel<CX, CY, RY, ST, h3::ARITH_FMA, true, MINB, XSW, true>;
     return v;
 }
 
 // compute region cx x cy (output tile (cx-4) x (cy-2)), rows/thread, stages, CTAs/SM.  First = default;
-// HEAT3D_T2_TUNE="cx,cy,ry,stages,ctas[,chunk_len[,sched]]" selects another (experiments).
+// HEAT3D_T2_TUNE="cx,cy,ry,stages,ctas[,chunk_len[,xmode]]" selects another (experiments; xmode defaults to the first
+// entry's).  Shared-memory access mode (kernels_t2.cuh): "_L" 0 = plain loads (round 1), "_S" 1 = swapped x-neighbour
+// loads at both levels, "_P" 2 = plain loads from the stage + parity-split mid plane, "_X" 3 = swapped loads from the
+// stage + parity-split mid plane (no bank conflicts left at either level).
 const std::vector<T2Variant>& t2_variants()
 {
     static const std::vector<T2Variant> v = {
-        // "_L" = schedule 1: only centre values live across iterations, which is what lets a thread own 4 rows inside
-        // 128 registers.  4 rows per thread = 12 % fewer shared-memory wavefronts per cell, the 64x32 region wastes
-        // less on the redundant ring (60x30 of 64x32 useful): +4 % at 512^3, +8 % at 1024^2 planes (sustained).
-        make_t2<64, 32, 4, 4, 2, 1>("t2_64x32_r4_s4_c2_L"),
-        make_t2<64, 32, 4, 3, 2, 1>("t2_64x32_r4_s3_c2_L"),
-        make_t2<64, 16, 4, 4, 3, 1>("t2_64x16_r4_s4_c3_L"),
-        make_t2<64, 16, 2, 4, 3, 1>("t2_64x16_r2_s4_c3_L"),
-        // "_P" = schedule 2: schedule 1 with the mid plane split by x parity (no gain measured)
         make_t2<64, 32, 4, 4, 2, 2>("t2_64x32_r4_s4_c2_P"),
-        // schedule 0: partial_xy of the newest plane kept in registers (first version of the kernel)
-        make_t2<64, 16, 2, 3, 2>("t2_64x16_r2_s3_c2"),
-        make_t2<64, 16, 2, 4, 2>("t2_64x16_r2_s4_c2"),
-        make_t2<64, 32, 2, 4, 1>("t2_64x32_r2_s4_c1"),
-        make_t2<128, 16, 2, 4, 1>("t2_128x16_r2_s4_c1"),
+        make_t2<64, 32, 4, 4, 2, 0>("t2_64x32_r4_s4_c2_L"),
+        make_t2<64, 32, 4, 4, 2, 3>("t2_64x32_r4_s4_c2_X"),
+        make_t2<64, 16, 2, 4, 3, 2>("t2_64x16_r2_s4_c3_P"),
+        // 512 threads, one CTA per SM: smaller redundant level-1 ring (124x30 / 60x62 of 128x32 / 64x64 useful); measured
+        // slower than two independent 256-thread CTAs per SM (one barrier domain of 16 warps), kept for experiments
+        make_t2<128, 32, 4, 4, 1, 2>("t2_128x32_r4_s4_c1_P"),
+        make_t2<64, 64, 4, 4, 1, 2>("t2_64x64_r4_s4_c1_P"),
     };
     return v;
 }
@@ -257,10 +256,17 @@ struct Slab {
     unsigned long long* peer_flags[2] = {nullptr, nullptr};
     unsigned long long* d_flags = nullptr;
     double* snap_dev = nullptr;              // device-side staging copy of the owned planes for async snapshots (lazily allocated)
+    size_t snap_dev_bytes = 0;
+    double* up_dev = nullptr;                // device-side landing buffer of an asynchronous upload (lazily allocated)
+    size_t up_dev_bytes = 0;
+    uint32_t up_a = 0, up_b = 0;             // owned global planes [up_a, up_b) staged there, empty when up_b <= up_a
+    cudaStream_t h2d = nullptr;              // its own stream: uploads, snapshots (copy) and stepping all overlap
+    cudaEvent_t ev_up = nullptr;
     unsigned long long* d_done = nullptr;    // end-chunk CTAs finished so far (device counter the exchange stream waits on)
     unsigned long long done_target = 0;      // value d_done reaches when every end chunk launched so far is in memory
     bool lower = false, upper = false;     // has a neighbouring slab below / above
     int za = 0, zb = 0;                    // local output plane range (owned ∩ global interior)
+    std::map<long long, std::array<int, 4>> plan_cache;   // guided chunk plans by launch shape (plan_chunks)
 };
 
 }  // namespace
@@ -273,6 +279,7 @@ struct heat3d_ctx {
     const TmaVariant* variant = nullptr;
     const T2Variant* variant2 = nullptr;   // set when temporal_k >= 2
     int t2_chunk = 64;
+    bool t2_guided = true;             // long-then-short chunk plan (plan_guided); off when a chunk length is forced
     bool use_tma = true;
     bool multi_process = false;
     int snap_buf = -1;                 // buffer an async snapshot is still reading, or -1
@@ -286,8 +293,10 @@ struct heat3d_ctx {
     bool graphs_ok = true;
     bool res_slot_prezeroed = false;   // pipelined convergence loop: residual slots are cleared off the compute stream
     bool store_mode = false;           // ghost planes are written by the stencil kernel itself into the neighbours' memory
+    bool peers_reachable = true;       // every slab can address its in-process neighbours' memory (same device or peer access)
     bool end_signal = false;           // stream memory operations available: single-launch steps with end-chunk signalling
     unsigned long long seq = 0;        // number of ghost exchanges issued so far (same on every process)
+    unsigned long long consumed_seq = 0;   // depth-4 blocks issued so far: the value neighbours publish once they have read their ghosts
     bool timing_pending = false;       // a call's ev_start/ev_stop have not been folded into tm yet
     uint32_t call_steps = 0;           // steps issued by the current/last call
 };
@@ -327,8 +336,57 @@ struct MirrorInfo {
     unsigned long long flag_value;
 };
 
+// Long-then-short split of `nzp` middle planes for a launch of ntiles CTAs per chunk on `slots` resident CTA slots.
+// Equal chunks leave a tail: the last, partly filled wave costs as much as a full one.  Model: CTAs are handed to free
+// slots in index order, a CTA of L output planes costs L + ovh plane-times (ovh = the seam planes it loads and computes
+// on top, plus its prologue); the makespan of every candidate (n_long chunks of L, then n_short equal short ones) is
+// simulated and the shortest wins.  `first_ctas` CTAs of `first_cost` (the end chunks) come before everything else.
+struct ChunkSplit { int len, n_long, len2, split; };   // split = planes covered by the long chunks
+
+ChunkSplit plan_guided(int nzp, long long ntiles, long long slots, long long first_ctas, double first_cost, double ovh, int max_len)
+{
+    ChunkSplit best = {nzp, 1, nzp, nzp};
+    double best_t = 1e300;
+    std::vector<double> heap;
+    auto makespan = [&](int L, int nl, int nzl, int L2, int ns) {
+        heap.assign((size_t)slots, 0.0);           // min-heap of slot free times
+        auto cmp = [](double a, double b) { return a > b; };
+        auto give = [&](double cost) {
+            std::pop_heap(heap.begin(), heap.end(), cmp);
+            heap.back() += cost;
+            std::push_heap(heap.begin(), heap.end(), cmp);
+        };
+        for (long long i = 0; i < first_ctas; ++i) give(first_cost);
+        int left = nzl;
+        for (int c = 0; c < nl; ++c) { const int n = std::min(L, left); left -= n; for (long long t = 0; t < ntiles; ++t) give(n + ovh); }
+        left = nzp - nzl;
+        for (int c = 0; c < ns; ++c) { const int n = std::min(L2, left); left -= n; for (long long t = 0; t < ntiles; ++t) give(n + ovh); }
+        return *std::max_element(heap.begin(), heap.end());
+    };
+    auto consider = [&](int L, int nl, int ns) {
+        const int nzl = std::min(nzp, L * nl);
+        const int rest = nzp - nzl;
+        if ((rest > 0) != (ns > 0)) return;
+        const int L2 = ns ? (rest + ns - 1) / ns : L;
+        if (ns && (L2 < 2 || L2 > L)) return;
+        const int ns_eff = ns ? (rest + L2 - 1) / L2 : 0;
+        const long long ctas = (long long)(nl + ns_eff) * ntiles;
+        // no schedule beats total work / slots: most candidates with many short chunks end here
+        const double bound = ((double)first_ctas * first_cost + (double)ntiles * (nzp + ovh * (nl + ns_eff))) / (double)slots;
+        if (bound >= best_t || ctas > 60000) return;
+        const double t = makespan(L, nl, nzl, L2, ns_eff);
+        if (t < best_t - 1e-9) { best_t = t; best = {L, nl, L2, nzl}; }
+    };
+    const int lmax = std::min(max_len, nzp);
+    // long candidates first: they set a good bound early
+    for (int L = lmax; L >= 2; L -= (L > 64 ? 4 : L > 16 ? 2 : 1))
+        for (int nl = 1; (nl - 1) * L < nzp; ++nl)
+            for (int ns = 0; ns <= 6; ++ns) consider(L, nl, ns);
+    return best;
+}
+
 long long plan_chunks(h3::TmaWork& w, int za, int zb, int ends, int end_len, int chunk_len, long long slots, Slab& s,
-                      const MirrorInfo* mi = nullptr)
+                      const MirrorInfo* mi = nullptr, bool guided = false)
 {
     const long long ntiles = (long long)w.ntx * w.nty;
     w.n_end = 0;
@@ -363,14 +421,33 @@ long long plan_chunks(h3::TmaWork& w, int za, int zb, int ends, int end_len, int
     }
     const int nzp = w.mid_zb - w.mid_za;
     long long nch = 0;
-    w.chunk_len = chunk_len;
-    if (nzp > 0) {
+    w.chunk_len = w.chunk_len2 = chunk_len;
+    w.mid_split = w.mid_zb;
+    w.n_long = 0;
+    if (nzp > 0 && guided) {
+        // cached per (planes, end chunks): the search runs once per distinct launch shape of a slab
+        const long long key = ((long long)nzp << 8) | (long long)(w.n_end << 4) | (end_len & 15);
+        auto it = s.plan_cache.find(key);
+        if (it == s.plan_cache.end()) {
+            static const double ovh = getenv("HEAT3D_T2_OVH") ? atof(getenv("HEAT3D_T2_OVH")) : 6.0;
+            static const int max_len = getenv("HEAT3D_T2_MAXLEN") ? atoi(getenv("HEAT3D_T2_MAXLEN")) : 160;
+            const ChunkSplit cs = plan_guided(nzp, ntiles, slots, ntiles * w.n_end, end_len + ovh, ovh, max_len);
+            it = s.plan_cache.emplace(key, std::array<int, 4>{cs.len, cs.n_long, cs.len2, cs.split}).first;
+        }
+        w.chunk_len = it->second[0];
+        w.n_long = it->second[1];
+        w.chunk_len2 = it->second[2];
+        w.mid_split = w.mid_za + it->second[3];
+        const int rest = w.mid_zb - w.mid_split;
+        nch = w.n_long + (rest > 0 ? (rest + w.chunk_len2 - 1) / w.chunk_len2 : 0);
+    } else if (nzp > 0) {
         nch = (nzp + chunk_len - 1) / chunk_len;
         if ((nch + w.n_end) * ntiles < slots) nch = (slots + ntiles - 1) / ntiles - w.n_end;
         if (nch < 1) nch = 1;
         if (nch > nzp) nch = nzp;
-        w.chunk_len = (int)((nzp + nch - 1) / nch);
+        w.chunk_len = w.chunk_len2 = (int)((nzp + nch - 1) / nch);
         nch = (nzp + w.chunk_len - 1) / w.chunk_len;
+        w.n_long = (int)nch;
     }
     if (ends && !mi) s.done_target += (unsigned long long)ntiles * w.n_end;
     return ntiles * (w.n_end + nch);
@@ -455,11 +532,13 @@ int launch_stencil_t2(heat3d_ctx* c, Slab& s, int src, int za, int zb, bool res,
     const int ar = c->p.arith == HEAT3D_ARITH_FMA ? 1 : 0;
     double* dst = s.buf[src ^ 1];
     h3::TmaWork w;
-    w.ntx = ((int)c->p.nx + (v.cx - 4) - 1) / (v.cx - 4);
-    w.nty = ((int)c->p.ny + (v.cy - 2) - 1) / (v.cy - 2);
+    // x tiles start at column 0 and must reach column nx-2; y tiles start at the first interior row
+    w.ntx = ((int)c->p.nx - 1 + (v.cx - 4) - 1) / (v.cx - 4);
+    w.nty = ((int)c->p.ny - 2 + (v.cy - 2) - 1) / (v.cy - 2);
     MirrorInfo mi;
     const bool mirrored = fill_mirror(c, s, src ^ 1, ends, mi);
-    const long long grid = plan_chunks(w, za, zb, ends, /*end_len=*/16, c->t2_chunk, (long long)s.num_sms * v.minb, s, mirrored ? &mi : nullptr);
+    const long long grid = plan_chunks(w, za, zb, ends, /*end_len=*/16, c->t2_chunk, (long long)s.num_sms * v.minb, s, mirrored ? &mi : nullptr,
+                                       c->t2_guided);
     int z1lo = (int)(1 - s.zg0), z1hi = (int)((long long)c->p.nz - 1 - s.zg0);   // level-1 planes that are global interior planes
     unsigned long long* first = res ? s.d_res_base + 2 : nullptr;     // residual of the first of the two updates
     void* args[] = {(void*)&s.tmap2[src], (void*)&dst, (void*)&g, (void*)&w, (void*)&z1lo, (void*)&z1hi, (void*)&s.d_res, (void*)&first};
@@ -479,7 +558,7 @@ Slab* local_slab(heat3d_ctx* c, int gidx)
 // Push the outermost G owned planes of buffer `b` into the neighbours' ghost planes of their buffer `b`
 // (same-process neighbours: peer copy; other processes: NCCL send/recv), on each slab's comm stream,
 // after that slab's ev_boundary.  Records ev_put per slab.
-int exchange_ghosts(heat3d_ctx* c, int b, bool after_counted_launch = false)
+int exchange_ghosts(heat3d_ctx* c, int b, bool after_counted_launch = false, unsigned long long consumed = 0)
 {
     bool any_nccl = false;
     c->seq++;
@@ -492,6 +571,16 @@ int exchange_ghosts(heat3d_ctx* c, int b, bool after_counted_launch = false)
             if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuStreamWaitValue64 failed with CUresult %d", (int)r);
         } else {
             CU_TRY(cudaStreamWaitEvent(s.comm, s.ev_boundary, 0));
+        }
+        if (consumed) {
+            // depth-4 blocks overwrite ghost planes of the buffer the neighbour's first pass is reading: wait until the
+            // neighbour says it has read them (it writes `consumed` into my flags after that pass, in stream order)
+            for (int side = 0; side < 2; ++side) {
+                if (!(side == 0 ? s.lower : s.upper)) continue;
+                if (!local_slab(c, s.gidx + (side == 0 ? -1 : 1)) && !s.ipc) continue;      // NCCL: the receiver posts the recv itself
+                CUresult r = g_stream_wait64((CUstream)s.comm, (CUdeviceptr)(s.d_flags + 2 + side), consumed, CU_STREAM_WAIT_VALUE_GEQ);
+                if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuStreamWaitValue64 failed with CUresult %d", (int)r);
+            }
         }
         const size_t bytes = (size_t)s.G * s.plane * sizeof(double);
         const uint32_t nzl = s.z1 - s.z0;
@@ -645,6 +734,55 @@ int step_block(heat3d_ctx* c, int k, bool res)
     return HEAT3D_OK;
 }
 
+// Communication-avoiding block of FOUR updates on a context with ghost depth 4: two depth-2 passes and ONE exchange.
+// Pass A advances the owned planes AND two ghost planes per neighbour side (their inputs, four ghost planes deep, are
+// all there), pass B advances the owned planes again from that; then the outer four owned planes travel.  Both passes
+// end in the buffer they started from, so `cur` does not change.  The exchange of this block overwrites, in the
+// neighbour, ghost planes that ITS pass A of the same block reads, and nothing else orders the two: every slab
+// publishes "consumed" to its neighbours after its pass A (a stream-ordered flag write) and puts wait for it.
+int step_block4(heat3d_ctx* c, bool res)
+{
+    const int src = c->cur, mid = c->cur ^ 1;
+    const unsigned long long seq_before = c->seq;
+    const unsigned long long round = ++c->consumed_seq;
+    for (Slab& s : c->slabs) {
+        int rc = set_dev(s);
+        if (rc) return rc;
+        if (c->snap_buf >= 0) CU_TRY(cudaStreamWaitEvent(s.compute, s.ev_snap, 0));
+        if (res && !c->res_slot_prezeroed) CU_TRY(cudaMemsetAsync(s.d_res, 0, sizeof(unsigned long long), s.compute));
+        if (res) CU_TRY(cudaMemsetAsync(s.d_res_base + 2, 0, sizeof(unsigned long long), s.compute));
+        if (!s.lower && !s.upper) {
+            if ((rc = launch_stencil_t2(c, s, src, s.za, s.zb, false, 0))) return rc;
+            if ((rc = launch_stencil_t2(c, s, mid, s.za, s.zb, res, 0))) return rc;
+            continue;
+        }
+        if (c->halo_timed) CU_TRY(cudaEventRecord(s.ev_wait0[c->call_steps % HALO_RING], s.compute));
+        if ((rc = wait_ghosts(c, s, seq_before))) return rc;
+        if (c->halo_timed) CU_TRY(cudaEventRecord(s.ev_wait1[c->call_steps % HALO_RING], s.compute));
+        if ((rc = launch_stencil_t2(c, s, src, s.lower ? s.za - 2 : s.za, s.upper ? s.zb + 2 : s.zb, false, 0))) return rc;
+        for (int side = 0; side < 2; ++side) {
+            if (!(side == 0 ? s.lower : s.upper) || !s.peer_flags[side]) continue;
+            // I am the upper neighbour of the slab below me (its flag [3]) and the lower neighbour of the one above (its flag [2])
+            CUresult r = g_stream_write64((CUstream)s.compute, (CUdeviceptr)(s.peer_flags[side] + 2 + (side == 0 ? 1 : 0)), round, 0);
+            if (r != CUDA_SUCCESS) return fail(HEAT3D_ERR_CUDA, "cuStreamWriteValue64 failed with CUresult %d", (int)r);
+        }
+        if ((rc = launch_stencil_t2(c, s, mid, s.za, s.zb, res, (s.lower ? 1 : 0) | (s.upper ? 2 : 0)))) return rc;
+    }
+    c->snap_buf = -1;
+    int rc = exchange_ghosts(c, src, /*after_counted_launch=*/true, round);
+    if (rc) return rc;
+    c->tm.steps += 4;
+    c->call_steps++;
+    return HEAT3D_OK;
+}
+
+// depth-4 blocks need slabs that talk (otherwise two depth-2 passes are the same thing) and stream memory operations
+bool use_block4(const heat3d_ctx* c)
+{
+    return c->p.temporal_k == 4 && c->variant2 && (c->slabs.size() > 1 || c->multi_process) && c->end_signal && !c->store_mode &&
+           c->peers_reachable && !(c->p.flags & HEAT3D_FLAG_NO_OVERLAP);
+}
+
 int finish_timing(heat3d_ctx* c);
 
 int begin_call(heat3d_ctx* c)
@@ -747,6 +885,9 @@ void destroy_slab(Slab& s)
         if (e) cudaEventDestroy(e);
     if (s.d_done) cudaFree(s.d_done);
     if (s.snap_dev) cudaFree(s.snap_dev);
+    if (s.up_dev) cudaFree(s.up_dev);
+    if (s.h2d) cudaStreamDestroy(s.h2d);
+    if (s.ev_up) cudaEventDestroy(s.ev_up);
     if (s.d_partial) cudaFree(s.d_partial);
     if (s.d_scalar) cudaFree(s.d_scalar);
     if (s.h_scalar) cudaFreeHost(s.h_scalar);
@@ -788,6 +929,8 @@ int setup_slab(heat3d_ctx* c, Slab& s)
         CU_TRY(cudaStreamCreateWithPriority(&s.comm, cudaStreamNonBlocking, hi));
     }
     CU_TRY(cudaStreamCreateWithFlags(&s.copy, cudaStreamNonBlocking));
+    CU_TRY(cudaStreamCreateWithFlags(&s.h2d, cudaStreamNonBlocking));
+    CU_TRY(cudaEventCreateWithFlags(&s.ev_up, cudaEventDisableTiming));
     cudaEvent_t* sync_evs[] = {&s.ev_boundary, &s.ev_put, &s.ev_snap, &s.ev_tmp};
     for (cudaEvent_t* e : sync_evs) CU_TRY(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     cudaEvent_t* time_evs[] = {&s.ev_start, &s.ev_stop};
@@ -807,8 +950,8 @@ int setup_slab(heat3d_ctx* c, Slab& s)
     CU_TRY(cudaMemset(s.d_done, 0, sizeof(unsigned long long)));
     CU_TRY(cudaMalloc(&s.d_side_done, 2 * sizeof(unsigned long long)));
     CU_TRY(cudaMemset(s.d_side_done, 0, 2 * sizeof(unsigned long long)));
-    CU_TRY(cudaMalloc(&s.d_flags, 2 * sizeof(unsigned long long)));
-    CU_TRY(cudaMemset(s.d_flags, 0, 2 * sizeof(unsigned long long)));
+    CU_TRY(cudaMalloc(&s.d_flags, 4 * sizeof(unsigned long long)));    // [0],[1] arrival from below / above; [2],[3] consumed by below / above
+    CU_TRY(cudaMemset(s.d_flags, 0, 4 * sizeof(unsigned long long)));
     CU_TRY(cudaMemset(s.d_res_base, 0, 3 * sizeof(unsigned long long)));
     s.partial_blocks = s.num_sms * 8;
     CU_TRY(cudaMalloc(&s.d_partial, (size_t)s.partial_blocks * sizeof(double)));
@@ -908,6 +1051,18 @@ int mp_barrier(heat3d_ctx* c)
     return HEAT3D_OK;
 }
 
+// compute + exchange streams only: snapshot (copy) and upload (h2d) transfers may keep running across this
+int sync_compute(heat3d_ctx* c)
+{
+    for (Slab& s : c->slabs) {
+        int rc = set_dev(s);
+        if (rc) return rc;
+        CU_TRY(cudaStreamSynchronize(s.compute));
+        CU_TRY(cudaStreamSynchronize(s.comm));
+    }
+    return HEAT3D_OK;
+}
+
 int check_ctx(const heat3d_ctx* c)
 {
     if (!c) return fail(HEAT3D_ERR_INVALID, "null context");
@@ -981,8 +1136,9 @@ int heat3d_create(const heat3d_params* pin, heat3d_ctx** out)
     if (p.nx > (1u << 30) || p.ny > (1u << 30) || p.nz > (1u << 30)) return fail(HEAT3D_ERR_INVALID, "grid axis too large");
     if (p.arith != HEAT3D_ARITH_STRICT && p.arith != HEAT3D_ARITH_FMA) return fail(HEAT3D_ERR_INVALID, "unknown arith %d", p.arith);
     if (p.temporal_k <= 0) p.temporal_k = 1;
-    if (p.temporal_k > 2) return fail(HEAT3D_ERR_INVALID, "temporal_k=%d not available in this build (1 or 2)", p.temporal_k);
-    if (p.temporal_k == 2 && p.kernel == HEAT3D_KERNEL_BASELINE) return fail(HEAT3D_ERR_INVALID, "temporal_k=2 needs the TMA kernels");
+    if (p.temporal_k != 1 && p.temporal_k != 2 && p.temporal_k != 4)
+        return fail(HEAT3D_ERR_INVALID, "temporal_k=%d not available (1, 2 or 4)", p.temporal_k);
+    if (p.temporal_k >= 2 && p.kernel == HEAT3D_KERNEL_BASELINE) return fail(HEAT3D_ERR_INVALID, "temporal_k=%d needs the TMA kernels", p.temporal_k);
     if (p.nslabs <= 0) p.nslabs = 1;
     if (p.nlocal <= 0) p.nlocal = p.nslabs;
     if (p.slab_first < 0 || p.slab_first + p.nlocal > p.nslabs) return fail(HEAT3D_ERR_INVALID, "slab range [%d,%d) outside [0,%d)", p.slab_first, p.slab_first + p.nlocal, p.nslabs);
@@ -1026,18 +1182,19 @@ int heat3d_create(const heat3d_params* pin, heat3d_ctx** out)
         }
     }
 
-    if (c->use_tma && p.temporal_k == 2) {
+    if (c->use_tma && p.temporal_k >= 2) {
         const auto& vs = t2_variants();
         c->variant2 = &vs[0];
         if (const char* e = getenv("HEAT3D_T2_TUNE")) {
-            int t[7] = {0, 0, 0, 0, 0, 0, 0};
+            int t[7] = {0, 0, 0, 0, 0, 0, vs[0].xmode};
             sscanf(e, "%d,%d,%d,%d,%d,%d,%d", &t[0], &t[1], &t[2], &t[3], &t[4], &t[5], &t[6]);
             c->variant2 = nullptr;
             for (const T2Variant& v : vs)
-                if (t[0] == v.cx && t[1] == v.cy && t[2] == v.ry && t[3] == v.stages && t[4] == v.minb && t[6] == v.sched) { c->variant2 = &v; break; }
+                if (t[0] == v.cx && t[1] == v.cy && t[2] == v.ry && t[3] == v.stages && t[4] == v.minb && t[6] == v.xmode) { c->variant2 = &v; break; }
             if (!c->variant2) { delete c; return fail(HEAT3D_ERR_INVALID, "no depth-2 kernel variant matches HEAT3D_T2_TUNE=%s", e); }
-            if (t[5] > 0) c->t2_chunk = t[5];
+            if (t[5] > 0) { c->t2_chunk = t[5]; c->t2_guided = false; }      // a forced chunk length means uniform chunks
         }
+        if (const char* e = getenv("HEAT3D_T2_GUIDED")) c->t2_guided = atoi(e) != 0;
     }
 
     if (p.nslabs > 1 && c->use_tma) {
@@ -1098,12 +1255,13 @@ int heat3d_create(const heat3d_params* pin, heat3d_ctx** out)
             s.peer_buf[side][1] = n->buf[1];
             s.peer_flags[side] = n->d_flags;
         }
+    c->peers_reachable = reachable;
     {
         // HEAT3D_EXCHANGE=store: the stencil kernel itself writes the outer planes into the neighbours' ghost planes
         // (peer stores over NVLink) and publishes their arrival - no copy, no exchange stream.  Needs every neighbour's
         // memory mapped here and slabs thick enough for two separate end chunks; otherwise the copy paths are used.
         const char* ex = getenv("HEAT3D_EXCHANGE");
-        bool ok = ex && strcmp(ex, "store") == 0 && p.nslabs > 1 && c->end_signal && c->use_tma && !(p.flags & HEAT3D_FLAG_NO_OVERLAP) &&
+        bool ok = ex && strcmp(ex, "store") == 0 && p.temporal_k != 4 && p.nslabs > 1 && c->end_signal && c->use_tma && !(p.flags & HEAT3D_FLAG_NO_OVERLAP) &&
                   reachable && (!multi_process || c->slabs[0].ipc);
         for (int g = 0; g < p.nslabs && ok; ++g) {      // same verdict on every process: look at all slabs, not just mine
             long long a = (long long)((uint64_t)g * p.nz / p.nslabs), b = (long long)((uint64_t)(g + 1) * p.nz / p.nslabs);
@@ -1189,6 +1347,7 @@ int heat3d_sync(heat3d_ctx* c)
         CU_TRY(cudaStreamSynchronize(s.compute));
         CU_TRY(cudaStreamSynchronize(s.comm));
         CU_TRY(cudaStreamSynchronize(s.copy));
+        CU_TRY(cudaStreamSynchronize(s.h2d));
     }
     return HEAT3D_OK;
 }
@@ -1210,7 +1369,10 @@ int heat3d_init_reference_field(heat3d_ctx* c, double sp_y)
     }
     c->cur = 0;
     c->have_res = false;
-    return heat3d_sync(c);
+    if ((rc = heat3d_sync(c))) return rc;
+    // One-sided exchanges (ipc-put, peer-store) write into the NEIGHBOUR's ghost planes, and the first step after an
+    // init waits for no arrival flag: nobody may start stepping before every process has finished rewriting its ghosts.
+    return mp_barrier(c);
 }
 
 int heat3d_upload_planes(heat3d_ctx* c, const double* host, uint32_t z0, uint32_t n)
@@ -1243,6 +1405,72 @@ int heat3d_upload_planes(heat3d_ctx* c, const double* host, uint32_t z0, uint32_
             if ((rc = exchange_ghosts(c, w))) return rc;
     c->have_res = false;
     return heat3d_sync(c);
+}
+
+int heat3d_upload_planes_async(heat3d_ctx* c, const double* host, uint32_t z0, uint32_t n)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (!host) return fail(HEAT3D_ERR_INVALID, "null host pointer");
+    if (z0 < c->slabs.front().z0 || z0 + n > c->slabs.back().z1)
+        return fail(HEAT3D_ERR_INVALID, "planes [%u,%u) outside this context's range [%u,%u)", z0, z0 + n, c->slabs.front().z0, c->slabs.back().z1);
+    const size_t plane_host = (size_t)c->p.nx * c->p.ny;
+    for (Slab& s : c->slabs) {
+        const uint32_t a = z0 > s.z0 ? z0 : s.z0, b = (z0 + n) < s.z1 ? (z0 + n) : s.z1;
+        s.up_a = s.up_b = 0;
+        if (b <= a) continue;
+        if ((rc = set_dev(s))) return rc;
+        const size_t bytes = (size_t)(s.z1 - s.z0) * s.plane * sizeof(double);
+        if (s.up_dev_bytes < bytes) {
+            if (s.up_dev) CU_TRY(cudaFree(s.up_dev));
+            s.up_dev = nullptr; s.up_dev_bytes = 0;
+            cudaError_t e = cudaMalloc(&s.up_dev, bytes);
+            if (e != cudaSuccess) return fail(HEAT3D_ERR_ALLOC, "cudaMalloc of %zu bytes for the upload landing buffer failed: %s", bytes, cudaGetErrorString(e));
+            s.up_dev_bytes = bytes;
+        }
+        // the landing buffer may still be the source of the previous commit's device-side copies
+        CU_TRY(cudaEventRecord(s.ev_tmp, s.compute));
+        CU_TRY(cudaStreamWaitEvent(s.h2d, s.ev_tmp, 0));
+        double* dev = s.up_dev + (size_t)(a - s.z0) * s.plane;
+        const double* src = host + (size_t)(a - z0) * plane_host;
+        const size_t rows = (size_t)c->p.ny * (b - a), row_bytes = (size_t)c->p.nx * 8;
+        if (s.pitch == c->p.nx) CU_TRY(cudaMemcpyAsync(dev, src, rows * row_bytes, cudaMemcpyHostToDevice, s.h2d));
+        else CU_TRY(cudaMemcpy2DAsync(dev, (size_t)s.pitch * 8, src, row_bytes, row_bytes, rows, cudaMemcpyHostToDevice, s.h2d));
+        CU_TRY(cudaEventRecord(s.ev_up, s.h2d));
+        s.up_a = a; s.up_b = b;
+    }
+    return HEAT3D_OK;
+}
+
+int heat3d_upload_commit(heat3d_ctx* c)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    bool any = false;
+    for (Slab& s : c->slabs) any = any || s.up_b > s.up_a;
+    if (!any) return fail(HEAT3D_ERR_STATE, "heat3d_upload_commit without a staged heat3d_upload_planes_async");
+    if ((rc = sync_compute(c))) return rc;
+    if ((rc = mp_barrier(c))) return rc;      // no neighbour may still be writing into the ghosts this call rewrites
+    for (Slab& s : c->slabs) {
+        if (s.up_b <= s.up_a) continue;
+        if ((rc = set_dev(s))) return rc;
+        CU_TRY(cudaStreamWaitEvent(s.compute, s.ev_up, 0));
+        const size_t off_up = (size_t)(s.up_a - s.z0) * s.plane, off_f = (size_t)(s.up_a - s.z0 + s.G) * s.plane;
+        const size_t bytes = (size_t)(s.up_b - s.up_a) * s.plane * sizeof(double);
+        for (int b = 0; b < 2; ++b)     // both buffers carry the Dirichlet shell
+            CU_TRY(cudaMemcpyAsync(s.buf[b] + off_f, s.up_dev + off_up, bytes, cudaMemcpyDeviceToDevice, s.compute));
+        s.up_a = s.up_b = 0;
+    }
+    for (Slab& s : c->slabs) {
+        if ((rc = set_dev(s))) return rc;
+        CU_TRY(cudaEventRecord(s.ev_boundary, s.compute));
+    }
+    if (c->slabs.size() > 1 || c->multi_process)
+        for (int w = 0; w < 2; ++w)
+            if ((rc = exchange_ghosts(c, w))) return rc;
+    c->have_res = false;
+    if ((rc = sync_compute(c))) return rc;
+    return mp_barrier(c);                     // ghosts of every process are in place before anybody steps
 }
 
 int heat3d_upload(heat3d_ctx* c, const double* host_global)
@@ -1289,6 +1517,8 @@ static int step_graph_blocks(heat3d_ctx* c, int k)
         const uint64_t steps0 = c->tm.steps, launches0 = c->tm.launches, lc0 = c->tm.last_call_launches,
                        ls0 = c->tm.last_call_stencil_launches;
         const uint32_t cs0 = c->call_steps;
+        const int cur0 = c->cur;
+        const unsigned long long seq0 = c->seq;
         cudaGraph_t graph = nullptr;
         if (cudaStreamBeginCapture(s.compute, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); return 1; }
         int rc = HEAT3D_OK;
@@ -1297,6 +1527,8 @@ static int step_graph_blocks(heat3d_ctx* c, int k)
         // capture only records work: undo the bookkeeping the recording did
         c->tm.steps = steps0; c->tm.launches = launches0; c->tm.last_call_launches = lc0; c->tm.last_call_stencil_launches = ls0;
         c->call_steps = cs0;
+        c->cur = cur0;          // GRAPH_BLOCKS is even, so a complete capture ends where it began; a failed one may not
+        c->seq = seq0;
         if (rc || e != cudaSuccess || !graph) { cudaGetLastError(); if (graph) cudaGraphDestroy(graph); return 1; }
         const cudaError_t ei = cudaGraphInstantiate(&exec, graph, 0);
         cudaGraphDestroy(graph);
@@ -1327,6 +1559,8 @@ static int advance_plain(heat3d_ctx* c, uint32_t nsteps)
             left -= (uint32_t)k * GRAPH_BLOCKS;
         }
     }
+    for (; use_block4(c) && left >= 4; left -= 4)
+        if ((rc = step_block4(c, force_res))) return rc;
     for (; c->variant2 && left >= 2; left -= 2)
         if ((rc = step_block(c, 2, force_res))) return rc;
     for (; left; --left)
@@ -1352,9 +1586,9 @@ int heat3d_step_residual(heat3d_ctx* c, uint32_t nsteps, double* residual)
     if (nsteps == 0) return fail(HEAT3D_ERR_INVALID, "nsteps must be >= 1 to produce a residual");
     if ((rc = begin_call(c))) return rc;
     // all but the last block plain; the last block (2 updates if that leaves an even count, else 1) carries the residual
-    const uint32_t last = (c->variant2 && nsteps >= 2 && nsteps % 2 == 0) ? 2u : 1u;
+    const uint32_t last = (use_block4(c) && nsteps >= 4 && nsteps % 4 == 0) ? 4u : (c->variant2 && nsteps >= 2 && nsteps % 2 == 0) ? 2u : 1u;
     if ((rc = advance_plain(c, nsteps - last))) return rc;
-    if ((rc = step_block(c, (int)last, true))) return rc;
+    if ((rc = last == 4 ? step_block4(c, true) : step_block(c, (int)last, true))) return rc;
     if ((rc = end_call(c))) return rc;
     return fetch_residual(c, residual);
 }
@@ -1373,7 +1607,7 @@ int heat3d_residual(heat3d_ctx* c, double* residual)
 // iteration i+1 is queued before the host looks at the residual of iteration i (two residual slots, two events).
 // If iteration i turns out to be the converging one, iteration i+1 is simply dropped: a depth-1 step never touches
 // the buffer it read from, so flipping `cur` back restores the state after iteration i exactly.
-static int run_every_iteration(heat3d_ctx* c, uint32_t iter_max, double eps, uint32_t* fin, int32_t* conv, uint32_t* done)
+static int run_every_iteration_loop(heat3d_ctx* c, uint32_t iter_max, double eps, uint32_t* fin, int32_t* conv, uint32_t* done)
 {
     int rc = begin_call(c);
     if (rc) return rc;
@@ -1432,12 +1666,20 @@ static int run_every_iteration(heat3d_ctx* c, uint32_t iter_max, double eps, uin
             break;
         }
     }
-    c->res_slot_prezeroed = false;
-    for (Slab& s : c->slabs) {      // later residual queries use slot 0 with their own clear on the compute stream
-        if ((rc = set_dev(s))) return rc;
-        CU_TRY(cudaStreamSynchronize(s.copy));
-    }
     return end_call(c);
+}
+
+static int run_every_iteration(heat3d_ctx* c, uint32_t iter_max, double eps, uint32_t* fin, int32_t* conv, uint32_t* done)
+{
+    const int rc = run_every_iteration_loop(c, iter_max, eps, fin, conv, done);
+    // on EVERY exit path, errors included: later residual queries use slot 0 and clear it themselves on the compute stream
+    c->res_slot_prezeroed = false;
+    for (Slab& s : c->slabs) {
+        s.d_res = s.d_res_base;
+        if (cudaSetDevice(s.dev) == cudaSuccess) cudaStreamSynchronize(s.copy);
+    }
+    if (rc) cudaGetLastError();
+    return rc;
 }
 
 // The same loop on a depth-2 context: one pass advances two iterations and its kernel reports BOTH residuals, so the
@@ -1582,7 +1824,12 @@ int heat3d_snapshot_async(heat3d_ctx* c, double* pinned)
         if ((rc = set_dev(s))) return rc;
         const uint32_t nzl = s.z1 - s.z0;
         const size_t bytes = (size_t)nzl * s.plane * sizeof(double);
-        if (!s.snap_dev && cudaMalloc(&s.snap_dev, bytes) != cudaSuccess) { cudaGetLastError(); s.snap_dev = nullptr; }
+        if (s.snap_dev_bytes < bytes) {
+            if (s.snap_dev) CU_TRY(cudaFree(s.snap_dev));
+            s.snap_dev = nullptr; s.snap_dev_bytes = 0;
+            if (cudaMalloc(&s.snap_dev, bytes) == cudaSuccess) s.snap_dev_bytes = bytes;
+            else { cudaGetLastError(); s.snap_dev = nullptr; }
+        }
         if (s.snap_dev) {
             // a device-to-device copy at HBM speed freezes the time level on the compute stream (milliseconds); the slow
             // trip over PCIe then reads the frozen copy on the copy stream and never holds a field buffer hostage
@@ -1603,6 +1850,57 @@ int heat3d_snapshot_async(heat3d_ctx* c, double* pinned)
         CU_TRY(cudaEventRecord(s.ev_snap, s.copy));
     }
     c->snap_buf = staged ? -1 : c->cur;
+    return HEAT3D_OK;
+}
+
+int heat3d_snapshot_strided_async(heat3d_ctx* c, double* pinned, uint32_t sx, uint32_t sy, uint32_t sz)
+{
+    int rc = check_ctx(c);
+    if (rc) return rc;
+    if (!pinned) return fail(HEAT3D_ERR_INVALID, "null host pointer");
+    if (sx == 0 || sy == 0 || sz == 0) return fail(HEAT3D_ERR_INVALID, "strides must be >= 1");
+    if (sx == 1 && sy == 1 && sz == 1) return heat3d_snapshot_async(c, pinned);
+    if ((rc = heat3d_snapshot_wait(c))) return rc;           // one snapshot in flight at a time
+    const uint32_t nxs = (c->p.nx + sx - 1) / sx, nys = (c->p.ny + sy - 1) / sy;
+    if (nys > 65535u * 32u) return fail(HEAT3D_ERR_INVALID, "too many output rows");
+    for (Slab& s : c->slabs) {
+        if ((rc = set_dev(s))) return rc;
+        const uint32_t zg_first = (s.z0 + sz - 1) / sz * sz;       // first owned global plane that is a multiple of sz
+        if (zg_first >= s.z1) continue;
+        const uint32_t np = (s.z1 - 1 - zg_first) / sz + 1;
+        const size_t bytes = (size_t)np * nys * nxs * sizeof(double);
+        if (s.snap_dev_bytes < bytes) {
+            if (s.snap_dev) CU_TRY(cudaFree(s.snap_dev));
+            s.snap_dev = nullptr; s.snap_dev_bytes = 0;
+            cudaError_t e = cudaMalloc(&s.snap_dev, bytes);
+            if (e != cudaSuccess) return fail(HEAT3D_ERR_ALLOC, "cudaMalloc of %zu bytes for the snapshot staging buffer failed: %s", bytes, cudaGetErrorString(e));
+            s.snap_dev_bytes = bytes;
+        }
+        // gather on the compute stream (freezes the time level, reads the field at HBM speed), PCIe copy on the copy stream
+        for (uint32_t p0 = 0; p0 < np; p0 += 65535u) {
+            const uint32_t n = std::min(65535u, np - p0);
+            h3::gather_strided_kernel<<<dim3(nys, n), 256, 0, s.compute>>>(s.buf[c->cur], s.snap_dev + (size_t)p0 * nys * nxs, (int)nxs, (int)nys,
+                                                                          (int)sx, (int)sy, (int)sz, (int)(zg_first - s.z0 + s.G + p0 * sz),
+                                                                          (int)s.pitch, s.plane);
+            CU_TRY(cudaGetLastError());
+            c->tm.launches++;
+        }
+        CU_TRY(cudaEventRecord(s.ev_tmp, s.compute));
+        CU_TRY(cudaStreamWaitEvent(s.copy, s.ev_tmp, 0));
+        CU_TRY(cudaMemcpyAsync(pinned + (size_t)(zg_first / sz) * nys * nxs, s.snap_dev, bytes, cudaMemcpyDeviceToHost, s.copy));
+        CU_TRY(cudaEventRecord(s.ev_snap, s.copy));
+    }
+    c->snap_buf = -1;       // the staging copy is the only thing the PCIe transfer reads
+    return HEAT3D_OK;
+}
+
+int heat3d_device_count(int32_t* count)
+{
+    if (!count) return fail(HEAT3D_ERR_INVALID, "null output");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) return fail(HEAT3D_ERR_CUDA, "cudaGetDeviceCount failed: %s (libheat3d has no CPU fallback)", cudaGetErrorString(e));
+    *count = n;
     return HEAT3D_OK;
 }
 

@@ -248,8 +248,10 @@ struct TmaWork {
     int ntx, nty;                 // tiles in x, y
     int n_end;                    // 0..2 end chunks, taken by CTAs [0, n_end * ntiles)
     int end_za[2], end_zb[2];     // their output plane ranges
-    int mid_za, mid_zb;           // the rest, cut into chunks of chunk_len
-    int chunk_len;
+    int mid_za, mid_zb;           // the rest: n_long chunks of chunk_len from mid_za up to mid_split, then chunks of
+    int chunk_len;                //           chunk_len2 up to mid_zb (long chunks first, short ones last: the launch's
+    int mid_split, n_long;        //           tail is made of short CTAs; mid_split == mid_zb means uniform chunks)
+    int chunk_len2;
     unsigned long long* done;     // copy-engine exchange: bumped once per finished end-chunk CTA; nullptr when nobody listens
     // Peer-store exchange (optional): end chunk i also writes the planes [mirror_z0[i], mirror_z1[i]) it produces straight
     // into the neighbouring slab's ghost planes (mirror[i] = the address local plane mirror_z0[i], row 0, column 0 maps
@@ -270,8 +272,14 @@ __device__ __forceinline__ bool chunk_of_cta(const TmaWork& w, int cidx, int& zs
         zs = cidx == 0 ? w.end_za[0] : w.end_za[1];
         cnt = (cidx == 0 ? w.end_zb[0] : w.end_zb[1]) - zs;
     } else {
-        zs = w.mid_za + (cidx - w.n_end) * w.chunk_len;
-        cnt = min(w.chunk_len, w.mid_zb - zs);
+        const int m = cidx - w.n_end;
+        if (m < w.n_long) {
+            zs = w.mid_za + m * w.chunk_len;
+            cnt = min(w.chunk_len, w.mid_split - zs);
+        } else {
+            zs = w.mid_split + (m - w.n_long) * w.chunk_len2;
+            cnt = min(w.chunk_len2, w.mid_zb - zs);
+        }
     }
     return is_end;
 }
@@ -388,6 +396,7 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
     constexpr int ROW = Cfg::ROW;
     static_assert(TX % 64 == 0 && TY % RY == 0 && NTHR % 32 == 0 && NTHR <= 1024, "tile shape");
     static_assert(STAGES >= 3, "the refill runs one plane behind the readers");
+    static_assert((NWARP & (NWARP - 1)) == 0, "the refill duty rotates over the warps with a mask");
 
     extern __shared__ __align__(128) unsigned char smem[];      // stages | full barriers | empty barriers
     uint64_t* full = (uint64_t*)(smem + STAGES * Cfg::STAGE_STRIDE);
@@ -536,6 +545,19 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
         cta_residual_commit(rmax, res_slot, (unsigned long long*)smem);
     }
     if (is_end && (w.done || (MIRROR && (w.side_done[0] || w.side_done[1])))) signal_end_chunk(w, cidx);
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Decimated snapshot: every sx-th / sy-th point of every listed plane, packed densely (x fastest) for the trip over
+// PCIe.  Plane p of the output is local plane zl0 + p*sz of the field.  One block per (output row, output plane).
+// ------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) gather_strided_kernel(const double* __restrict__ f, double* __restrict__ out, int nxs, int nys,
+                                                             int sx, int sy, int sz, int zl0, int pitch, long long plane)
+{
+    const int j = blockIdx.x, p = blockIdx.y;
+    const double* row = f + (long long)(zl0 + (long long)p * sz) * plane + (long long)j * sy * pitch;
+    double* o = out + ((long long)p * nys + j) * nxs;
+    for (int i = threadIdx.x; i < nxs; i += 256) o[i] = row[(long long)i * sx];
 }
 
 // ------------------------------------------------------------------------------------------------------

@@ -3,17 +3,33 @@
 // Same z-streaming skeleton as stencil_tma_kernel (kernels.cuh), with a second stencil level stacked on the
 // first inside the CTA:
 //   level 0  planes of time n arrive by TMA, box (CX+4) x (CY+2), exactly as in the depth-1 kernel;
-//   level 1  every thread finishes its 2 x RY patch of the time n+1 plane over the whole CX x CY compute region
+//   level 1  every thread forms its 2 x RY patch of the time n+1 plane over the whole CX x CY compute region
 //            (Dirichlet cells and Dirichlet planes are carried over unchanged, as the reference never updates
 //            them), keeps the centre values in registers and publishes the plane to a double-buffered shared
 //            "mid" plane;
-//   level 2  after one CTA barrier each thread reads the xy neighbours of its level-1 cells from the mid plane
-//            and finishes the time n+2 plane over the inner (CX-4) x (CY-2) region, which is what goes to HBM.
-// Each level uses the split partial_xy / finish_z evaluation, so every cell sees exactly the operations, in
-// exactly the order, of two separate depth-1 sweeps: results are bit-identical to stepping twice.
-// HBM traffic is one read + one write per cell per TWO updates (8 B per cell-update); the price is the
-// redundant level-1 ring (CX*CY / ((CX-4)*(CY-2)) of the level-1 work) and one barrier per plane.  The barrier
-// also tells the refill thread that the stage just read is free, so this kernel needs no empty barriers.
+//   level 2  one iteration later each thread reads the xy neighbours of its level-1 cells from the mid plane
+//            and forms the time n+2 plane over the inner (CX-4) x (CY-2) region, which is what goes to HBM.
+// Nothing but centre values lives across iterations: a staged plane stays resident one iteration longer and the
+// whole update of plane p-1 is formed when plane p has arrived (both levels), which is what lets a thread own 4 rows
+// inside 128 registers.  Every cell sees exactly the operations, in exactly the order, of two separate depth-1
+// sweeps (heat3D.cu:128-131 twice): results are bit-identical to stepping twice.
+// HBM traffic is one read + one write per cell per TWO updates (8 B per cell-update); the price is the redundant
+// level-1 ring (CX*CY / ((CX-4)*(CY-2)) of the level-1 work) and one CTA barrier per plane.  The barrier also tells
+// the refill thread that the older stage is free, so this kernel needs no empty barriers.
+//
+// Shared-memory access modes (template XMODE).  A thread's x neighbours are 8-byte words at a 16-byte lane stride: read
+// straight, a warp touches only half of the banks and every such load costs 4 wavefronts instead of 2 (ncu, round 1:
+// LSU data pipe at 77 %, a third of its wavefronts bank conflicts).  Two remedies, selectable per level:
+//   bit 0 (staged planes, level 1): "swapped" loads - lanes 8-15 and 24-31 fetch their RIGHT neighbour with the
+//          instruction that gives lanes 0-7 and 16-23 their LEFT one (and the other way round with the second
+//          instruction), so the 16 lanes that share a wavefront cover all 32 banks; two selects per value put the
+//          words back in place (TMA writes the stage, so its layout cannot change);
+//   bit 1 (mid plane, level 2): the mid plane is stored split by x parity (even-x cells in one array, odd-x cells in
+//          another), so left / right neighbours are 8-byte words at consecutive lanes - no selects, two 64-bit stores
+//          instead of one 128-bit store per row.
+// Measured (profiles/r02_*): removing the conflicts takes the LSU pipe from 77 % to 56 % but the selects cost issue
+// slots; the kernel is then co-limited by FP64 issue (2 cycles per warp instruction, 208 per thread and plane) and
+// instruction issue, see DESIGN.md.
 #pragma once
 #include "kernels.cuh"
 
@@ -37,29 +53,6 @@ struct T2Plan {
     StorePlan st;         // level-2 stores: inside the CTA's output tile AND domain-interior
 };
 
-// finish plane p-1 of one level (-> o) and start plane p (t, tw) from its centre values cn and xy neighbours
-template <int RY, int ARITH, bool FINISH, bool PARTIAL>
-__device__ __forceinline__ void level_step(const double2 (&cn)[RY], const double (&xl)[RY], const double (&xr)[RY], const double2& up,
-                                           const double2& dn, const double2 (&cp2)[RY], double2 (&t)[RY], double2 (&tw)[RY],
-                                           double2 (&o)[RY], double Dx, double Dy, double Dz)
-{
-#pragma unroll
-    for (int r = 0; r < RY; ++r) {
-        if (FINISH) {
-            o[r].x = finish_z2<ARITH>(t[r].x, tw[r].x, cp2[r].x, cn[r].x, Dz);
-            o[r].y = finish_z2<ARITH>(t[r].y, tw[r].y, cp2[r].y, cn[r].y, Dz);
-        }
-        if (PARTIAL) {
-            const double2 ym = r == 0 ? up : cn[r - 1];
-            const double2 yp = r == RY - 1 ? dn : cn[r + 1];
-            tw[r].x = twice(cn[r].x);
-            tw[r].y = twice(cn[r].y);
-            t[r].x = partial_xy2<ARITH>(cn[r].x, tw[r].x, xl[r], cn[r].y, ym.x, yp.x, Dx, Dy);
-            t[r].y = partial_xy2<ARITH>(cn[r].y, tw[r].y, cn[r].x, xr[r], ym.y, yp.y, Dx, Dy);
-        }
-    }
-}
-
 // whole update of one plane in one go (same operations, same order as partial_xy2 followed by finish_z2)
 template <int RY, int ARITH>
 __device__ __forceinline__ void level_full(const double2 (&c)[RY], const double (&xl)[RY], const double (&xr)[RY], const double2& up,
@@ -78,36 +71,56 @@ __device__ __forceinline__ void level_full(const double2 (&c)[RY], const double 
     }
 }
 
-// xy neighbours of a thread's 2 x RY patch, read from the staged plane.  SHFL = take the x neighbours from the
-// adjacent lanes' registers by warp shuffle instead (edge lanes still read the halo column): the kernel is bound
-// by shared-memory wavefronts (ncu: l1tex 80 %), and a strided 8-byte load costs 4 wavefronts per warp, but the four
-// 32-bit shuffles per row it takes to replace them turned out slower on B200 (profiles/r01_sweep_k2_shfl.txt).
-template <int RY, bool SHFL>
-__device__ __forceinline__ void load_neighbours(const double* __restrict__ S, int row_pitch, const double2 (&cn)[RY], int lane,
-                                                double (&xl)[RY], double (&xr)[RY], double2& up, double2& dn)
+// xy neighbours of a thread's 2 x RY patch, read from a staged (or mid) plane; S points at the thread's first cell.
+// XSW: `swp` lanes (8-15, 24-31) load right-then-left, the others left-then-right, see the header comment.
+// one lane of a converged warp (the PTX way to say "somebody do this once"; lets ptxas keep the TMA issue on the uniform path)
+__device__ __forceinline__ bool elect_one_sync()
+{
+    uint32_t pred;
+    asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(pred));
+    return pred != 0;
+}
+
+template <int RY, bool XSW>
+__device__ __forceinline__ void load_neighbours(const double* __restrict__ S, int row_pitch, bool swp, double (&xl)[RY], double (&xr)[RY],
+                                                double2& up, double2& dn)
 {
     up = *(const double2*)(S - row_pitch);
     dn = *(const double2*)(S + RY * row_pitch);
+    if (XSW) {
+        const double* A = S + (swp ? 2 : -1);
+        const double* B = S + (swp ? -1 : 2);
 #pragma unroll
-    for (int r = 0; r < RY; ++r) {
-        if (SHFL) {
-            xl[r] = __shfl_up_sync(0xffffffffu, cn[r].y, 1);
-            xr[r] = __shfl_down_sync(0xffffffffu, cn[r].x, 1);
-            if (lane == 0) xl[r] = S[r * row_pitch - 1];
-            if (lane == 31) xr[r] = S[r * row_pitch + 2];
-        } else {
+        for (int r = 0; r < RY; ++r) {
+            const double a = A[r * row_pitch], b = B[r * row_pitch];
+            xl[r] = swp ? b : a;
+            xr[r] = swp ? a : b;
+        }
+    } else {
+#pragma unroll
+        for (int r = 0; r < RY; ++r) {
             xl[r] = S[r * row_pitch - 1];
             xr[r] = S[r * row_pitch + 2];
         }
     }
 }
 
-// SCHED 0: each level keeps partial_xy of its newest plane in registers and finishes it when the next plane shows up.
-// SCHED 1: nothing but centre values lives across iterations: a staged plane stays resident one iteration longer and
-//          the whole update of plane p-1 is formed when plane p has arrived (level 1), likewise for level 2 from the
-//          previous mid plane.  Same arithmetic, ~32 fewer registers per thread.
-// SCHED 2: schedule 1 with the mid plane stored split by x parity (cheaper x-neighbour loads at level 2).
-template <int CX, int CY, int RY, int STAGES, int ARITH, bool RES, int MINB, int SCHED, bool MIRROR>
+// the same from a mid plane stored split by x parity: E / O point at the thread's even / odd cell of its first row,
+// MP = words per row of one parity array
+template <int RY>
+__device__ __forceinline__ void load_neighbours_split(const double* __restrict__ E, const double* __restrict__ O, int MP, double (&xl)[RY],
+                                                      double (&xr)[RY], double2& up, double2& dn)
+{
+    up = make_double2(E[-MP], O[-MP]);
+    dn = make_double2(E[RY * MP], O[RY * MP]);
+#pragma unroll
+    for (int r = 0; r < RY; ++r) {
+        xl[r] = O[r * MP - 1];      // the odd cell of the pair to the left: consecutive lanes, consecutive words
+        xr[r] = E[r * MP + 1];      // the even cell of the pair to the right
+    }
+}
+
+template <int CX, int CY, int RY, int STAGES, int ARITH, bool RES, int MINB, int XMODE, bool MIRROR>
 __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     stencil_tma_t2_kernel(const __grid_constant__ CUtensorMap tmap, double* __restrict__ dst, Geom g, TmaWork w, int z1lo, int z1hi,
                           unsigned long long* res_slot, unsigned long long* res_slot_first)
@@ -116,12 +129,8 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     constexpr int NTHR = (CX / 2) * (CY / RY);
     constexpr int NWARP = NTHR / 32;
     constexpr int ROW = Cfg::ROW;
-#ifdef HEAT3D_T2_SHFL_X
-    constexpr bool SHFL_X = true;      // measured on B200: 433 GLUPS vs 536 with shared-memory loads - left off
-#else
-    constexpr bool SHFL_X = false;
-#endif
-    static_assert(CX % 64 == 0 && CY % RY == 0 && NTHR % 32 == 0 && NTHR <= 1024 && STAGES >= 2 + (SCHED ? 1 : 0), "tile shape");
+    static_assert(CX % 64 == 0 && CY % RY == 0 && NTHR % 32 == 0 && NTHR <= 1024 && STAGES >= 3, "tile shape");
+    static_assert((NWARP & (NWARP - 1)) == 0, "the refill duty rotates over the warps with a mask");
 
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* mid = smem + STAGES * Cfg::STAGE_STRIDE;
@@ -135,7 +144,8 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     const bool is_end = chunk_of_cta(w, cidx, zs, cnt);
     if (cnt <= 0) return;
     const int niter = cnt + 4;                                  // input planes zs-2 .. zs+cnt+1
-    const int ox = (tile % w.ntx) * Cfg::OX, oy = (tile / w.ntx) * Cfg::OY;   // output tile origin
+    // output tile origin: x tiles start at column 0 (pairs stay 16-byte aligned), y tiles at the first interior row
+    const int ox = (tile % w.ntx) * Cfg::OX, oy = 1 + (tile / w.ntx) * Cfg::OY;
     const int bx = ox - 4, by = oy - 2;                         // TMA box origin
 
     if (tid == 0) {
@@ -154,9 +164,16 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
 
     const int lx = tid % (CX / 2);
     const int ry = tid / (CX / 2);
-    const int warp = tid >> 5, lane = tid & 31;
+    const int lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);     // known to be warp-uniform: branches on it stay uniform
+    const bool swp = (lane >> 3) & 1;
+    constexpr bool XSW1 = (XMODE & 1) != 0;                     // swapped x-neighbour loads from the staged planes
+    constexpr bool MIDP = (XMODE & 2) != 0;                     // mid plane split by x parity
     const int gx = ox - 2 + 2 * lx;                             // global x of this thread's first cell
     const int gy = oy - 1 + ry * RY;                            // global y of this thread's first row
+    // A warp is one 64-cell run of RY rows.  Warps that lie wholly outside the domain (partial tiles at the high
+    // edges) only keep the barriers and the refill duty: their cells feed nothing that is stored.
+    const bool active = gy <= g.ny - 1 && (ox - 2 + 2 * (lx & ~31)) <= g.nx - 1;
     T2Plan pl;
     pl.i1x0 = gx >= 1 && gx <= g.nx - 2;
     pl.i1x1 = gx + 1 >= 1 && gx + 1 <= g.nx - 2;
@@ -180,189 +197,149 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     int zout = zs;
     auto mir_now = [&]() -> double* { return (MIRROR && mir && zout >= mz0 && zout < mz1) ? mir : nullptr; };
     const int soff = (1 + ry * RY) * ROW + 2 + 2 * lx;
-    // SCHED 2 stores the mid plane split by x parity: a thread's left / right x neighbours are then 8-byte words at
-    // consecutive lanes (2 wavefronts per warp load) instead of the second halves of 16-byte pairs (4 wavefronts).
-    constexpr int MP = CX / 2 + 2;                       // words per row of one parity array (one halo pair each side)
-    constexpr int MHALF = (CY + 2) * MP;                 // one parity array; two of them fit one STAGE_STRIDE
+    constexpr int MP = CX / 2 + 2;                       // split mid plane: words per row of one parity array (a halo word each side)
+    constexpr int MHALF = (CY + 2) * MP;                 // one parity array; both fit one mid buffer
     static_assert(2 * MHALF * 8 <= Cfg::STAGE_STRIDE, "split mid plane must fit the mid buffer");
     const int moff = (1 + ry * RY) * MP + 1 + lx;
+    // Warp-uniform shortcuts.  Level 1: no lane of the warp holds a Dirichlet cell.  Level 2 stores: every lane stores
+    // whole pairs or nothing (true for all warps but those that hold the domain's first / last interior column), so a
+    // row is one predicated 128-bit store and the warp never splits over the store code.
+    const bool warp_all1 = __all_sync(0xffffffffu, pl.all1);
+    const bool warp_pairs = __all_sync(0xffffffffu, pl.st.x0 == pl.st.x1);
+    const uint32_t pair_rows = pl.st.x0 ? pl.st.rows : 0u;
     double rmax = 0.0;      // residual of the second update (time n+1 -> n+2), over the cells this CTA stores
     double rmax1 = 0.0;     // residual of the first update (time n -> n+1), over every level-1 cell this CTA forms: cells
                             // shared with neighbouring CTAs are counted more than once, which a maximum does not mind
 
-    double2 C0[3][RY], t0[RY], tw0[RY];      // level 0: centres of the last three planes, partial / 2*centre of the newest
-    double2 C1[3][RY], t1[RY], tw1[RY];      // level 1: same
+    double2 C0[3][RY];      // level 0: centres of the last three staged planes
+    double2 C1[3][RY];      // level 1: centres of the last three time n+1 planes
 #pragma unroll
-    for (int r = 0; r < RY; ++r) t0[r] = tw0[r] = t1[r] = tw1[r] = C1[0][r] = C1[1][r] = C1[2][r] = make_double2(0.0, 0.0);
+    for (int r = 0; r < RY; ++r) C0[0][r] = C0[1][r] = C0[2][r] = C1[0][r] = C1[1][r] = C1[2][r] = make_double2(0.0, 0.0);
 
-    uint32_t s = 0, ph = 0;
-    int par = 0;
-
-    // One input plane.  q = index of the plane inside the chunk's input run; the level-1 plane finished here is
-    // local plane zs + q - 3, the level-2 plane finished here is zs + q - 4.
-    auto body = [&](int q, double2 (&c0n)[RY], const double2 (&c0p1)[RY], const double2 (&c0p2)[RY], double2 (&c1n)[RY],
-                    const double2 (&c1p1)[RY], const double2 (&c1p2)[RY]) {
-        const double* S = (const double*)(smem + s * Cfg::STAGE_STRIDE) + soff;
-        mbar_wait(&full[s], ph);
-        double xl[RY], xr[RY];
-        double2 up, dn;
-#pragma unroll
-        for (int r = 0; r < RY; ++r) c0n[r] = *(const double2*)(S + r * ROW);
-        load_neighbours<RY, SHFL_X>(S, ROW, c0n, lane, xl, xr, up, dn);
-
-        // ---- level 1: finish plane q-1 of the input run, start plane q
-        if (q >= 2) level_step<RY, ARITH, true, true>(c0n, xl, xr, up, dn, c0p2, t0, tw0, c1n, g.Dx, g.Dy, g.Dz);
-        else if (q == 1) level_step<RY, ARITH, false, true>(c0n, xl, xr, up, dn, c0p2, t0, tw0, c1n, g.Dx, g.Dy, g.Dz);
-        if (q >= 2) {
-            const int z1 = zs + q - 3;
-            const bool zint = z1 >= z1lo && z1 < z1hi;
-            if (!(zint && pl.all1)) {           // Dirichlet cells / planes keep their value
-#pragma unroll
-                for (int r = 0; r < RY; ++r) {
-                    const bool row = zint && ((pl.rows1 >> r) & 1u);
-                    if (!(row && pl.i1x0)) c1n[r].x = c0p1[r].x;
-                    if (!(row && pl.i1x1)) c1n[r].y = c0p1[r].y;
-                }
-            }
-            if (RES) {
-#pragma unroll
-                for (int r = 0; r < RY; ++r) {
-                    res_track(rmax1, c1n[r].x, c0p1[r].x);
-                    res_track(rmax1, c1n[r].y, c0p1[r].y);
-                }
-            }
-            double* M = (double*)(mid + par * Cfg::STAGE_STRIDE) + soff;
-#pragma unroll
-            for (int r = 0; r < RY; ++r) *(double2*)(M + r * ROW) = c1n[r];
-        }
-        __syncthreads();        // the stage has been read by everyone; the mid plane is complete
-        if (warp == (q & (NWARP - 1)) && lane == 0 && q + STAGES < niter) {
-            mbar_arrive_expect_tx(&full[s], Cfg::STAGE_BYTES);
-            tma_load_3d(smem + s * Cfg::STAGE_STRIDE, &tmap, &full[s], bx, by, zs - 2 + q + STAGES);
-        }
-        if (++s == STAGES) { s = 0; ph ^= 1u; }
-
-        // ---- level 2: finish plane (zs+q-4), start plane (zs+q-3)
-        if (q >= 3) {
-            const double* M = (const double*)(mid + par * Cfg::STAGE_STRIDE) + soff;
-            load_neighbours<RY, SHFL_X>(M, ROW, c1n, lane, xl, xr, up, dn);
-            double2 o[RY];
-            if (q >= 4) level_step<RY, ARITH, true, true>(c1n, xl, xr, up, dn, c1p2, t1, tw1, o, g.Dx, g.Dy, g.Dz);
-            else level_step<RY, ARITH, false, true>(c1n, xl, xr, up, dn, c1p2, t1, tw1, o, g.Dx, g.Dy, g.Dz);
-            if (q >= 4) {
-                double* const mnow = mir_now();
-#pragma unroll
-                for (int r = 0; r < RY; ++r) {
-                    store_pair(out + (long long)r * g.pitch, mnow ? mnow + (long long)r * g.pitch : nullptr, o[r], pl.st, r);
-                    if (RES) res_pair(rmax, o[r], c1p1[r], pl.st, r);
-                }
-                out += g.plane;
-                if (MIRROR) { if (mir) mir += g.plane; ++zout; }
+    // The per-plane CTA barrier is a named barrier (id 1) so that warps with nothing to compute can take part in it from
+    // a loop of their own instead of dragging a predicate through the compute loop.
+    auto plane_barrier = [] { asm volatile("bar.sync 1, %0;" ::"n"(NTHR) : "memory"); };
+    // after the barrier of iteration q: plane q-1's stage is free, refill it with plane q-1+STAGES.  The duty rotates over
+    // the warps; `warp` is a warp-uniform value and the issuing lane is elected, so the seven warps whose turn it is not
+    // pay one uniform compare-and-branch.
+    auto refill = [&](int q, uint32_t sprev) {
+        if (warp == (q & (NWARP - 1)) && q >= 1 && q - 1 + STAGES < niter) {
+            if (elect_one_sync()) {
+                mbar_arrive_expect_tx(&full[sprev], Cfg::STAGE_BYTES);
+                tma_load_3d(smem + sprev * Cfg::STAGE_STRIDE, &tmap, &full[sprev], bx, by, zs - 2 + q - 1 + STAGES);
             }
         }
-        par ^= 1;
     };
 
-    // SCHED 1 body.  Input plane q sits in stage q % STAGES, plane q-1 is still in the previous stage.
-    auto body1 = [&](int q, double2 (&c0n)[RY], const double2 (&c0p1)[RY], const double2 (&c0p2)[RY], double2 (&c1n)[RY],
-                     const double2 (&c1p1)[RY], const double2 (&c1p2)[RY]) {
-        const uint32_t sprev = s == 0 ? STAGES - 1 : s - 1;
-        const double* S = (const double*)(smem + s * Cfg::STAGE_STRIDE) + soff;
-        const double* Sp = (const double*)(smem + sprev * Cfg::STAGE_STRIDE) + soff;
-        mbar_wait(&full[s], ph);
-#pragma unroll
-        for (int r = 0; r < RY; ++r) c0n[r] = *(const double2*)(S + r * ROW);
-        double xl[RY], xr[RY];
-        double2 up, dn;
-        if (q >= 2) {   // level 1: plane q-1 of the run = local plane zs + q - 3
-            load_neighbours<RY, false>(Sp, ROW, c0p1, lane, xl, xr, up, dn);
-            level_full<RY, ARITH>(c0p1, xl, xr, up, dn, c0p2, c0n, c1n, g.Dx, g.Dy, g.Dz);
-            const int z1 = zs + q - 3;
-            const bool zint = z1 >= z1lo && z1 < z1hi;
-            if (!(zint && pl.all1)) {           // Dirichlet cells / planes keep their value
-#pragma unroll
-                for (int r = 0; r < RY; ++r) {
-                    const bool row = zint && ((pl.rows1 >> r) & 1u);
-                    if (!(row && pl.i1x0)) c1n[r].x = c0p1[r].x;
-                    if (!(row && pl.i1x1)) c1n[r].y = c0p1[r].y;
+    auto run = [&] {
+        uint32_t s = 0, ph = 0;
+        int par = 0;
+            // One input plane.  q = index of the plane inside the chunk's input run: it sits in stage q % STAGES, plane q-1 is
+            // still in the previous stage.  The level-1 plane formed here is local plane zs + q - 3, the level-2 plane zs + q - 4.
+            auto body = [&](int q, double2 (&c0n)[RY], const double2 (&c0p1)[RY], const double2 (&c0p2)[RY], double2 (&c1n)[RY],
+                            const double2 (&c1p1)[RY], const double2 (&c1p2)[RY]) {
+                const uint32_t sprev = s == 0 ? STAGES - 1 : s - 1;
+                const double* S = (const double*)(smem + s * Cfg::STAGE_STRIDE) + soff;
+                const double* Sp = (const double*)(smem + sprev * Cfg::STAGE_STRIDE) + soff;
+                mbar_wait(&full[s], ph);
+    #pragma unroll
+                for (int r = 0; r < RY; ++r) c0n[r] = *(const double2*)(S + r * ROW);
+                double xl[RY], xr[RY];
+                double2 up, dn;
+                if (q >= 2) {   // level 1: plane q-1 of the run = local plane zs + q - 3
+                    load_neighbours<RY, XSW1>(Sp, ROW, swp, xl, xr, up, dn);
+                    level_full<RY, ARITH>(c0p1, xl, xr, up, dn, c0p2, c0n, c1n, g.Dx, g.Dy, g.Dz);
+                    const int z1 = zs + q - 3;
+                    const bool zint = z1 >= z1lo && z1 < z1hi;
+                    if (!(zint && warp_all1)) {         // Dirichlet cells / planes keep their value
+    #pragma unroll
+                        for (int r = 0; r < RY; ++r) {
+                            const bool row = zint && ((pl.rows1 >> r) & 1u);
+                            if (!(row && pl.i1x0)) c1n[r].x = c0p1[r].x;
+                            if (!(row && pl.i1x1)) c1n[r].y = c0p1[r].y;
+                        }
+                    }
+                    if (RES) {
+    #pragma unroll
+                        for (int r = 0; r < RY; ++r) {
+                            res_track(rmax1, c1n[r].x, c0p1[r].x);
+                            res_track(rmax1, c1n[r].y, c0p1[r].y);
+                        }
+                    }
+                    if (MIDP) {
+                        double* ME = (double*)(mid + par * Cfg::STAGE_STRIDE) + moff;
+                        double* MO = ME + MHALF;
+    #pragma unroll
+                        for (int r = 0; r < RY; ++r) {
+                            ME[r * MP] = c1n[r].x;
+                            MO[r * MP] = c1n[r].y;
+                        }
+                    } else {
+                        double* M = (double*)(mid + par * Cfg::STAGE_STRIDE) + soff;
+    #pragma unroll
+                        for (int r = 0; r < RY; ++r) *(double2*)(M + r * ROW) = c1n[r];
+                    }
                 }
-            }
-            if (RES) {
-#pragma unroll
-                for (int r = 0; r < RY; ++r) {
-                    res_track(rmax1, c1n[r].x, c0p1[r].x);
-                    res_track(rmax1, c1n[r].y, c0p1[r].y);
+                if (q >= 4) {   // level 2: local plane zs + q - 4, from the mid plane published one iteration ago
+                    if (MIDP) {
+                        const double* ME = (const double*)(mid + (par ^ 1) * Cfg::STAGE_STRIDE) + moff;
+                        load_neighbours_split<RY>(ME, ME + MHALF, MP, xl, xr, up, dn);
+                    } else {
+                        const double* Mp = (const double*)(mid + (par ^ 1) * Cfg::STAGE_STRIDE) + soff;
+                        load_neighbours<RY, XSW1>(Mp, ROW, swp, xl, xr, up, dn);
+                    }
+                    double2 o[RY];
+                    level_full<RY, ARITH>(c1p1, xl, xr, up, dn, c1p2, c1n, o, g.Dx, g.Dy, g.Dz);
+                    double* const mnow = mir_now();
+                    if (warp_pairs && !(MIRROR && mnow)) {      // the common case: one predicated 128-bit store per row
+    #pragma unroll
+                        for (int r = 0; r < RY; ++r)
+                            if ((pair_rows >> r) & 1u) *(double2*)(out + (long long)r * g.pitch) = o[r];
+                    } else {
+    #pragma unroll
+                        for (int r = 0; r < RY; ++r)
+                            store_pair(out + (long long)r * g.pitch, mnow ? mnow + (long long)r * g.pitch : nullptr, o[r], pl.st, r);
+                    }
+                    if (RES) {
+    #pragma unroll
+                        for (int r = 0; r < RY; ++r) res_pair(rmax, o[r], c1p1[r], pl.st, r);
+                    }
+                    out += g.plane;
+                    if (MIRROR) { if (mir) mir += g.plane; ++zout; }
                 }
-            }
-            if (SCHED == 2) {   // even-x cells and odd-x cells in separate arrays (see MP below)
-                double* ME = (double*)(mid + par * Cfg::STAGE_STRIDE) + moff;
-                double* MO = ME + MHALF;
-#pragma unroll
-                for (int r = 0; r < RY; ++r) {
-                    ME[r * MP] = c1n[r].x;
-                    MO[r * MP] = c1n[r].y;
-                }
-            } else {
-                double* M = (double*)(mid + par * Cfg::STAGE_STRIDE) + soff;
-#pragma unroll
-                for (int r = 0; r < RY; ++r) *(double2*)(M + r * ROW) = c1n[r];
-            }
+                plane_barrier();        // plane q-1's stage has been read by everyone; this iteration's mid plane is complete
+                refill(q, sprev);
+                if (++s == STAGES) { s = 0; ph ^= 1u; }
+                par ^= 1;
+            };
+
+
+        // Register rotation: level 0 newest = C0[q % 3]; level 1 newest (plane q-1 of the run) = C1[(q + 2) % 3].
+        body(0, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
+        body(1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
+        body(2, C0[2], C0[1], C0[0], C1[1], C1[0], C1[2]);
+        int q = 3;
+        for (; q + 2 < niter; q += 3) {
+            body(q, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
+            body(q + 1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
+            body(q + 2, C0[2], C0[1], C0[0], C1[1], C1[0], C1[2]);
         }
-        if (q >= 4) {   // level 2: local plane zs + q - 4, from the mid plane published one iteration ago
-            if (SCHED == 2) {
-                const double* ME = (const double*)(mid + (par ^ 1) * Cfg::STAGE_STRIDE) + moff;
-                const double* MO = ME + MHALF;
-                up = make_double2(ME[-MP], MO[-MP]);
-                dn = make_double2(ME[RY * MP], MO[RY * MP]);
-#pragma unroll
-                for (int r = 0; r < RY; ++r) {
-                    xl[r] = MO[r * MP - 1];      // the odd cell of the pair to the left: consecutive lanes, consecutive words
-                    xr[r] = ME[r * MP + 1];      // the even cell of the pair to the right
-                }
-            } else {
-                const double* Mp = (const double*)(mid + (par ^ 1) * Cfg::STAGE_STRIDE) + soff;
-                load_neighbours<RY, false>(Mp, ROW, c1p1, lane, xl, xr, up, dn);
-            }
-            double2 o[RY];
-            level_full<RY, ARITH>(c1p1, xl, xr, up, dn, c1p2, c1n, o, g.Dx, g.Dy, g.Dz);
-            double* const mnow = mir_now();
-#pragma unroll
-            for (int r = 0; r < RY; ++r) {
-                store_pair(out + (long long)r * g.pitch, mnow ? mnow + (long long)r * g.pitch : nullptr, o[r], pl.st, r);
-                if (RES) res_pair(rmax, o[r], c1p1[r], pl.st, r);
-            }
-            out += g.plane;
-            if (MIRROR) { if (mir) mir += g.plane; ++zout; }
+        if (q < niter) {
+            body(q, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
+            if (q + 1 < niter) body(q + 1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
         }
-        __syncthreads();        // plane q-1's stage has been read by everyone; this iteration's mid plane is complete
-        if (q >= 1 && warp == (q & (NWARP - 1)) && lane == 0 && q - 1 + STAGES < niter) {
-            mbar_arrive_expect_tx(&full[sprev], Cfg::STAGE_BYTES);
-            tma_load_3d(smem + sprev * Cfg::STAGE_STRIDE, &tmap, &full[sprev], bx, by, zs - 2 + q - 1 + STAGES);
-        }
-        if (++s == STAGES) { s = 0; ph ^= 1u; }
-        par ^= 1;
     };
 
-    // Register rotation: level 0 newest = C0[q % 3]; level 1 newest (plane q-1 of the run) = C1[(q + 2) % 3].
-#define H3_T2_BODY(qq, a, b, c, d, e, f)                                  \
-    do {                                                                  \
-        if (SCHED >= 1) body1(qq, a, b, c, d, e, f);                      \
-        else body(qq, a, b, c, d, e, f);                                  \
-    } while (0)
-    H3_T2_BODY(0, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
-    H3_T2_BODY(1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
-    H3_T2_BODY(2, C0[2], C0[1], C0[0], C1[1], C1[0], C1[2]);
-    int q = 3;
-    for (; q + 2 < niter; q += 3) {
-        H3_T2_BODY(q, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
-        H3_T2_BODY(q + 1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
-        H3_T2_BODY(q + 2, C0[2], C0[1], C0[0], C1[1], C1[0], C1[2]);
+    if (!active) {      // nothing to compute: keep the barriers and take the refill turns
+        uint32_t s = 0;
+        for (int q = 0; q < niter; ++q) {
+            plane_barrier();
+            refill(q, s == 0 ? STAGES - 1 : s - 1);
+            if (++s == STAGES) s = 0;
+        }
+    } else {
+        run();
     }
-    if (q < niter) {
-        H3_T2_BODY(q, C0[0], C0[2], C0[1], C1[2], C1[1], C1[0]);
-        if (q + 1 < niter) H3_T2_BODY(q + 1, C0[1], C0[0], C0[2], C1[0], C1[2], C1[1]);
-    }
-#undef H3_T2_BODY
     if (RES) {
         __syncthreads();
         cta_residual_commit(rmax, res_slot, (unsigned long long*)smem);

@@ -25,6 +25,9 @@
 
 #include <cuda_runtime.h>
 
+#include <atomic>
+#include <climits>
+
 namespace {
 
 constexpr int MAX_DEVICES = 64;
@@ -33,7 +36,10 @@ constexpr int MAX_DEVICES = 64;
 // the address is fetched per device below and handed to the kernels as an ordinary pointer.
 static __device__ __align__(256) double g_plane_partials[HEAT3D_NOALLOC_MAX_PLANES];
 
-double* g_partials_addr[MAX_DEVICES] = {};   // device address of g_plane_partials on each device, once known
+// device address of g_plane_partials on each device, once known.  Per process and per primary context: after a
+// cudaDeviceReset the cached value is stale.  Atomic because first calls may come from several host threads (they all
+// resolve the same address, so a lost race only repeats the look-up).
+std::atomic<double*> g_partials_addr[MAX_DEVICES];
 
 template <int BLOCK>
 __device__ __forceinline__ double block_sum(double v)
@@ -85,6 +91,8 @@ extern "C" int heat3d_mean_abs_error_vs_y_noalloc(const double* d_field, uint32_
     if (!d_field || !d_err) return h3::set_last_error(HEAT3D_ERR_INVALID, "null device pointer");
     if (nx < 3 || ny < 3 || nz < 3) return h3::set_last_error(HEAT3D_ERR_INVALID, "grid %ux%ux%u: every axis needs >= 3 points", nx, ny, nz);
     if (pitch_doubles < nx) return h3::set_last_error(HEAT3D_ERR_INVALID, "row pitch %u doubles is shorter than nx=%u", pitch_doubles, nx);
+    if (nx > (uint32_t)INT_MAX || ny > (uint32_t)INT_MAX || pitch_doubles > (uint32_t)INT_MAX)
+        return h3::set_last_error(HEAT3D_ERR_INVALID, "nx=%u, ny=%u, pitch=%u: each must fit a 32-bit signed int", nx, ny, pitch_doubles);
     const uint32_t planes = nz - 2;
     if (planes > HEAT3D_NOALLOC_MAX_PLANES)
         return h3::set_last_error(HEAT3D_ERR_INVALID,
@@ -95,18 +103,19 @@ extern "C" int heat3d_mean_abs_error_vs_y_noalloc(const double* d_field, uint32_
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return h3::set_last_error(HEAT3D_ERR_CUDA, "cudaGetDevice failed: %s (libheat3d has no CPU fallback)", cudaGetErrorString(e));
     if (dev < 0 || dev >= MAX_DEVICES) return h3::set_last_error(HEAT3D_ERR_INVALID, "device ordinal %d not supported here", dev);
-    if (!g_partials_addr[dev]) {
+    double* partials = g_partials_addr[dev].load(std::memory_order_acquire);
+    if (!partials) {
         // once per device, with that device current: the host-side symbol is not an address a kernel can use
-        double* addr = nullptr;
-        e = cudaGetSymbolAddress((void**)&addr, g_plane_partials);
-        if (e != cudaSuccess || !addr)
+        e = cudaGetSymbolAddress((void**)&partials, g_plane_partials);
+        if (e != cudaSuccess || !partials)
             return h3::set_last_error(HEAT3D_ERR_CUDA, "cudaGetSymbolAddress(scratch) on device %d failed: %s", dev, cudaGetErrorString(e));
-        g_partials_addr[dev] = addr;
+        g_partials_addr[dev].store(partials, std::memory_order_release);
     }
-    double* partials = g_partials_addr[dev];
     cudaStream_t st = (cudaStream_t)stream;
     // same divisor as the reference: an `unsigned` product (heat3D.cu:1102), kept with its wrap-around
     const unsigned count = (nx - 2u) * (ny - 2u) * (nz - 2u);
+    if (count == 0u)
+        return h3::set_last_error(HEAT3D_ERR_INVALID, "(nx-2)(ny-2)(nz-2) wraps to 0 in the reference's 32-bit divisor for %ux%ux%u", nx, ny, nz);
     plane_abs_error_kernel<<<planes, 256, 0, st>>>(d_field, (int)nx, (int)ny, (long long)pitch_doubles,
                                                    (long long)pitch_doubles * ny, sp_y, partials);
     fold_partials_kernel<<<1, 256, 0, st>>>(partials, (int)planes, 1.0 / (double)count, d_err);

@@ -55,6 +55,8 @@ EXPORTS = {
     "heat3d_download": (C.c_int, [_ctx, _dp]),
     "heat3d_upload_planes": (C.c_int, [_ctx, _dp, C.c_uint32, C.c_uint32]),
     "heat3d_download_planes": (C.c_int, [_ctx, _dp, C.c_uint32, C.c_uint32]),
+    "heat3d_upload_planes_async": (C.c_int, [_ctx, _dp, C.c_uint32, C.c_uint32]),
+    "heat3d_upload_commit": (C.c_int, [_ctx]),
     "heat3d_local_range": (C.c_int, [_ctx, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "heat3d_step": (C.c_int, [_ctx, C.c_uint32]),
     "heat3d_step_residual": (C.c_int, [_ctx, C.c_uint32, _dp]),
@@ -66,6 +68,8 @@ EXPORTS = {
                                                      C.c_void_p, C.c_void_p]),
     "heat3d_snapshot_async": (C.c_int, [_ctx, _dp]),
     "heat3d_snapshot_wait": (C.c_int, [_ctx]),
+    "heat3d_snapshot_strided_async": (C.c_int, [_ctx, _dp, C.c_uint32, C.c_uint32, C.c_uint32]),
+    "heat3d_device_count": (C.c_int, [C.POINTER(C.c_int32)]),
     "heat3d_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
     "heat3d_host_free": (C.c_int, [C.c_void_p]),
     "heat3d_sync": (C.c_int, [_ctx]),
@@ -215,6 +219,13 @@ class Heat3D:
     def upload_planes(self, T, z0):
         _check(lib().heat3d_upload_planes(self._ctx, self._arr(T, T.shape[0]), z0, T.shape[0]))
 
+    def upload_planes_async(self, T_pinned, z0):
+        """Start the host->device copy of pinned planes; install them with upload_commit()."""
+        _check(lib().heat3d_upload_planes_async(self._ctx, self._arr(T_pinned, T_pinned.shape[0]), z0, T_pinned.shape[0]))
+
+    def upload_commit(self):
+        _check(lib().heat3d_upload_commit(self._ctx))
+
     def download_planes(self, z0, n, out=None):
         out = np.empty((n, self.ny, self.nx)) if out is None else out
         _check(lib().heat3d_download_planes(self._ctx, self._arr(out, n), z0, n))
@@ -261,6 +272,12 @@ class Heat3D:
         base = pinned_local.ctypes.data - z0 * self.ny * self.nx * 8
         _check(lib().heat3d_snapshot_async(self._ctx, C.cast(C.c_void_p(base), _dp)))
 
+    def snapshot_strided_async(self, pinned, sx, sy, sz):
+        """Decimated snapshot into a pinned array of shape (ceil(nz/sz), ceil(ny/sy), ceil(nx/sx))."""
+        shape = (-(-self.nz // sz), -(-self.ny // sy), -(-self.nx // sx))
+        assert pinned.dtype == np.float64 and pinned.flags["C_CONTIGUOUS"] and pinned.shape == shape, (pinned.shape, shape)
+        _check(lib().heat3d_snapshot_strided_async(self._ctx, pinned.ctypes.data_as(_dp), sx, sy, sz))
+
     def snapshot_wait(self):
         _check(lib().heat3d_snapshot_wait(self._ctx))
 
@@ -297,6 +314,12 @@ def mean_abs_error_vs_y_noalloc(d_field_ptr, nx, ny, nz, pitch_doubles, sp_y, d_
     """heat3d_mean_abs_error_vs_y_noalloc on the caller's own device buffers (raw addresses); queues work on
     `stream` and returns - synchronise before reading d_err.  Allocates nothing; see include/heat3d.h for the limits."""
     _check(lib().heat3d_mean_abs_error_vs_y_noalloc(d_field_ptr, nx, ny, nz, pitch_doubles, sp_y, d_err_ptr, stream))
+
+
+def device_count():
+    n = C.c_int32()
+    _check(lib().heat3d_device_count(C.byref(n)))
+    return n.value
 
 
 def slab_bounds(nz, nslabs):

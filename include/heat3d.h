@@ -67,8 +67,10 @@ typedef struct heat3d_params {
     uint32_t nx, ny, nz;        /* global point counts (cu:332-335), each >= 3                             */
     double Dx, Dy, Dz;          /* dt*alpha/sp^2 as the caller derives them (cu:359-367)                  */
     int32_t arith;              /* HEAT3D_ARITH_*                                                          */
-    int32_t temporal_k;         /* FTCS updates fused per HBM pass = ghost depth: 1 (0 means 1) or 2; results are
-                                   bit-identical either way                                                */
+    int32_t temporal_k;         /* ghost depth: 1 (0 means 1), 2 or 4; results are bit-identical in every case.
+                                   2: two FTCS updates fused per HBM pass (temporal blocking), one ghost exchange per pass.
+                                   4: the same kernel, communication-avoiding: blocks of four updates = two passes and ONE
+                                      exchange of four planes per side (the first pass also advances two ghost planes)  */
     int32_t kernel;             /* HEAT3D_KERNEL_*                                                         */
     int32_t nslabs;             /* total z-slabs over all processes; 0/1 = single slab                     */
     int32_t slab_first;         /* first slab owned by this context                                        */
@@ -130,6 +132,16 @@ int heat3d_download(heat3d_ctx* ctx, double* host_global);
 int heat3d_upload_planes(heat3d_ctx* ctx, const double* host_planes, uint32_t z0, uint32_t nplanes);
 int heat3d_download_planes(heat3d_ctx* ctx, double* host_planes, uint32_t z0, uint32_t nplanes);
 
+/* Streaming variant of heat3d_upload_planes for callers that feed one field after another: _async starts the
+ * host->device copy of PINNED host memory on a stream of its own into a landing buffer (allocated on first use, one
+ * slab's worth per GPU) and returns at once - the copy overlaps heat3d_step calls already queued and a snapshot in
+ * flight; heat3d_upload_commit waits for it and installs the planes as the current time level (device-side copies
+ * into both buffers + ghost refresh; collective in a multi-process run).  One staged upload at a time; `host_planes`
+ * must stay valid until the commit.  Together with heat3d_snapshot_async this keeps PCIe busy in both directions
+ * while the GPU steps, where the reference copied the whole field both ways around every single update (cu:686-697). */
+int heat3d_upload_planes_async(heat3d_ctx* ctx, const double* pinned_host_planes, uint32_t z0, uint32_t nplanes);
+int heat3d_upload_commit(heat3d_ctx* ctx);
+
 /* Global plane range [*z0, *z1) owned by this context. */
 int heat3d_local_range(const heat3d_ctx* ctx, uint32_t* z0, uint32_t* z1);
 
@@ -187,6 +199,13 @@ int heat3d_mean_abs_error_vs_y_noalloc(const double* d_field, uint32_t nx, uint3
 int heat3d_snapshot_async(heat3d_ctx* ctx, double* pinned_host_global);
 int heat3d_snapshot_wait(heat3d_ctx* ctx);
 
+/* Decimated variant for grids whose full dump is not practical (the reference's text format is 61 bytes per point,
+ * cu:1165-1177: 65 GB at 1024^3): every sx-th / sy-th / sz-th point (indices 0, s, 2s, ...) of the current time level
+ * is packed on the device and only the packed array crosses PCIe.  `pinned_host_strided` is the dense decimated GLOBAL
+ * array [ceil(nz/sz)][ceil(ny/sy)][ceil(nx/sx)], x fastest; a context writes the planes it owns.  Same rules as
+ * heat3d_snapshot_async (one in flight; heat3d_snapshot_wait).  Strides (1,1,1) are heat3d_snapshot_async. */
+int heat3d_snapshot_strided_async(heat3d_ctx* ctx, double* pinned_host_strided, uint32_t sx, uint32_t sy, uint32_t sz);
+
 /* Pinned host allocation helpers (cudaHostAlloc / cudaFreeHost). */
 int heat3d_host_alloc(void** out, size_t bytes);
 int heat3d_host_free(void* p);
@@ -204,6 +223,10 @@ int heat3d_layout(const heat3d_ctx* ctx, int32_t local_slab, uint32_t* pitch_dou
 
 const char* heat3d_last_error(void);
 int heat3d_version(void);
+
+/* Number of CUDA devices this process can use (the reference asks cudaGetDeviceCount every step, cu:650-654); lets a
+ * host-only caller such as the heat3D driver map ranks to devices without linking the CUDA runtime itself. */
+int heat3d_device_count(int32_t* count);
 
 /* Name of the stencil kernel variant the context dispatches to (static string). */
 const char* heat3d_kernel_name(const heat3d_ctx* ctx);

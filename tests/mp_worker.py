@@ -62,8 +62,8 @@ def main():
         local = int(os.environ.get("LOCAL_RANK", rank))
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        for kernel, tk, exchange in ((2, 1, "ipc-put"), (2, 2, "ipc-put"), (2, 1, "peer-store"), (2, 2, "peer-store"), (2, 2, "nccl"),
-                                     (1, 1, "nccl")):
+        for kernel, tk, exchange in ((2, 1, "ipc-put"), (2, 2, "ipc-put"), (2, 4, "ipc-put"), (2, 1, "peer-store"), (2, 2, "peer-store"),
+                                     (2, 2, "nccl"), (2, 4, "nccl"), (1, 1, "nccl")):
             os.environ["HEAT3D_EXCHANGE"] = {"nccl": "nccl", "ipc-put": "ipc", "peer-store": "store"}[exchange]
             box = [h3.nccl_unique_id() if rank == 0 else None]      # a bootstrap id serves ONE communicator
             dist.broadcast_object_list(box, src=0)

@@ -189,6 +189,27 @@ def test_snapshot_async_overlaps_stepping(h3, oracle):
         assert np.array_equal(later, _oracle_field(oracle, nx, ny, nz, 17))
 
 
+@pytest.mark.parametrize("P", [1, 3])
+def test_strided_snapshot_matches_decimated_oracle(h3, oracle, P):
+    """heat3d_snapshot_strided_async packs every (sx,sy,sz)-th point on the device; the pinned array must be the
+    oracle's field decimated the same way, while stepping continues underneath."""
+    nx, ny, nz = 64, 48, 41
+    with h3.Heat3D(nx, ny, nz, nslabs=P, devices=[0] * P) as sim:
+        sim.init_reference_field()
+        sim.step(10)
+        for sx, sy, sz in ((2, 3, 4), (1, 1, 5), (7, 1, 1), (1, 1, 1)):
+            snap = h3.pinned_empty((-(-nz // sz), -(-ny // sy), -(-nx // sx)))
+            snap[:] = -1.0
+            sim.snapshot_strided_async(snap, sx, sy, sz)
+            sim.step(3)
+            sim.snapshot_wait()
+            want = _oracle_field(oracle, nx, ny, nz, 10)[::sz, ::sy, ::sx]
+            assert np.array_equal(snap, want), (sx, sy, sz)
+            sim.init_reference_field()
+            sim.step(10)
+    assert h3.device_count() >= 1
+
+
 def test_large_grid_properties(h3):
     """BASELINE config-2 size (512^3): size-independent checks instead of an oracle run —
     x<->z transpose symmetry and x/z reflection symmetry to rounding, max principle, monotone residual."""
@@ -208,7 +229,7 @@ def test_large_grid_properties(h3):
     assert t["steps"] == 100 and t["launches"] >= 100
 
 
-@pytest.mark.parametrize("k", [1, 2])
+@pytest.mark.parametrize("k", [1, 2, 4])
 def test_multi_device_one_process_bitwise(h3, oracle, k):
     """Slabs on distinct GPUs driven by one context (cudaMemcpyPeerAsync between devices)."""
     import torch

@@ -9,9 +9,9 @@ import pytest
 
 pytestmark = pytest.mark.gpu
 
-# cx,cy,rows/thread,stages,CTAs/SM[,chunk_len,schedule]
-T2_TUNES = ["64,32,4,4,2,7,1", "64,32,4,3,2,7,1", "64,16,4,4,3,7,1", "64,16,2,4,3,7,1", "64,32,4,4,2,7,2",
-            "64,16,2,3,2", "64,16,2,4,2", "64,32,2,4,1", "128,16,2,4,1"]
+# cx,cy,rows/thread,stages,CTAs/SM,chunk_len,xmode  (shared-memory access mode, kernels_t2.cuh: 0 "_L" plain loads,
+# 1 "_S" swapped x-neighbour loads, 2 "_P" parity-split mid plane, 3 "_X" both)
+T2_TUNES = ["64,32,4,4,2,7,2", "64,32,4,4,2,7,0", "64,32,4,4,2,7,3", "64,16,2,4,3,7,2", "128,32,4,4,1,7,2", "64,64,4,4,1,7,2"]
 
 
 @pytest.fixture(scope="module")
@@ -51,11 +51,11 @@ def test_depth2_bit_exact_vs_oracle(h3, oracle, shape, nsteps):
 def test_every_depth2_variant(h3, oracle, tune):
     nx, ny, nz, nsteps = 150, 70, 41, 10
     f = tune.split(",")
-    os.environ["HEAT3D_T2_TUNE"] = tune if len(f) > 5 else tune + ",7"        # short chunks: several chunk seams inside the grid
+    os.environ["HEAT3D_T2_TUNE"] = tune        # chunk_len 7: several chunk seams inside the grid
     ref = _oracle_field(oracle, nx, ny, nz, nsteps)
     prev = _oracle_field(oracle, nx, ny, nz, nsteps - 1)
     with h3.Heat3D(nx, ny, nz, temporal_k=2) as sim:
-        assert sim.kernel_name() == "t2_%sx%s_r%s_s%s_c%s" % tuple(f[:5]) + ({"1": "_L", "2": "_P"}.get(f[6], "") if len(f) > 6 else "")
+        assert sim.kernel_name() == "t2_%sx%s_r%s_s%s_c%s" % tuple(f[:5]) + {"0": "_L", "1": "_S", "2": "_P", "3": "_X"}[f[6]]
         sim.init_reference_field()
         res = sim.step_residual(nsteps)               # even count: the residual comes out of the depth-2 kernel
         got = sim.download()
@@ -118,18 +118,21 @@ def test_depth2_multi_slab_equals_single_domain_bitwise(h3, oracle, shape, P, ns
         assert res == oracle.residual(ref, prev)
 
 
-def test_depth2_large_grid_matches_depth1(h3):
-    """512^3: the depth-2 path against the depth-1 path of the same library, bit for bit, after an odd step count."""
-    n, nsteps = 512, 21
-    with h3.Heat3D(n, n, n) as a:
-        a.init_reference_field()
-        a.step(nsteps)
-        A = a.download()
-    with h3.Heat3D(n, n, n, temporal_k=2) as b:
-        b.init_reference_field()
-        b.step(nsteps)
-        B = b.download()
-    assert np.array_equal(A, B)
+@pytest.mark.parametrize("guided", ["1", "0"])
+def test_depth2_guided_chunk_plan_and_partial_tiles(h3, oracle, guided):
+    """The default launch plan (long chunks first, short ones last) against uniform chunks, on a grid with partial tiles
+    at the high x and y edges (warps that lie wholly outside the domain sit out the compute loop) and enough planes for
+    several chunk seams."""
+    nx, ny, nz, nsteps = 129, 95, 300, 6
+    os.environ["HEAT3D_T2_GUIDED"] = guided
+    try:
+        ref = _oracle_field(oracle, nx, ny, nz, nsteps)
+        with h3.Heat3D(nx, ny, nz, temporal_k=2) as sim:
+            sim.init_reference_field()
+            sim.step(nsteps)
+            assert np.array_equal(sim.download(), ref)
+    finally:
+        os.environ.pop("HEAT3D_T2_GUIDED", None)
 
 
 @pytest.mark.parametrize("k", [1, 2])
@@ -207,3 +210,39 @@ def test_depth2_first_update_residual_matches_oracle(h3, oracle):
         sim.step(8)
         assert sim.step_residual(2) == oracle.residual(c2, b)       # the second update's residual is what this call returns
         assert np.array_equal(sim.download(), c2)
+
+
+@pytest.mark.parametrize("shape,P,nsteps", [((40, 24, 31), 2, 20), ((21, 13, 34), 4, 27), ((70, 40, 29), 3, 13), ((33, 17, 33), 8, 9),
+                                            ((150, 70, 64), 4, 16)])
+def test_depth4_blocks_multi_slab_equal_single_domain_bitwise(h3, oracle, shape, P, nsteps):
+    """temporal_k=4: ghost depth 4, blocks of four updates = two depth-2 passes and ONE exchange (the first pass also
+    advances two ghost planes per side).  Same bar as every other decomposition: bit-identical to the single domain -
+    with step counts that leave depth-2 and depth-1 tails, residuals out of the last block, uploads, and the
+    every-iteration convergence loop (which exchanges after every pass)."""
+    nx, ny, nz = shape
+    _, _, D = oracle.coefficients(nx, ny, nz)
+    ref = _oracle_field(oracle, nx, ny, nz, nsteps)
+    prev = _oracle_field(oracle, nx, ny, nz, nsteps - 1)
+    with h3.Heat3D(nx, ny, nz, temporal_k=4, nslabs=P, devices=[0] * P, flags=h3.FLAG_TIME_HALO) as sim:
+        assert sim.layout()[2] == 4
+        sim.init_reference_field()
+        res = sim.step_residual(nsteps)
+        assert np.array_equal(sim.download(), ref)
+        assert res == oracle.residual(ref, prev)
+        sim.step(8)                                    # two whole blocks on top
+        assert np.array_equal(sim.download(), _oracle_field(oracle, nx, ny, nz, nsteps + 8))
+        res8 = sim.step_residual(8)                    # residual out of a depth-4 block
+        want = _oracle_field(oracle, nx, ny, nz, nsteps + 16)
+        assert np.array_equal(sim.download(), want)
+        assert res8 == oracle.residual(want, _oracle_field(oracle, nx, ny, nz, nsteps + 15))
+        T = np.random.default_rng(4).random((nz, ny, nx))
+        sim.upload(T)
+        sim.step(11)
+        assert np.array_equal(sim.download(), oracle.steps(T.copy(), D, 11))
+        sim.init_reference_field()
+        assert sim.run(13, 1e-30, check_every=1) == (13, 0, False)
+        assert np.array_equal(sim.download(), _oracle_field(oracle, nx, ny, nz, 13))
+    with h3.Heat3D(nx, ny, nz, temporal_k=4) as one:   # a single slab has nobody to talk to: plain depth-2 passes
+        one.init_reference_field()
+        one.step(nsteps)
+        assert np.array_equal(one.download(), ref)

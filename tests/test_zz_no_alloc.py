@@ -22,11 +22,14 @@ def h3():
     return ge.load_package()
 
 
-def _expected(h3, T):
+def _expected(h3, T, oracle=None):
     nz, ny, nx = T.shape
     with h3.Heat3D(nx, ny, nz) as sim:
         sim.upload(T)
-        return sim.mean_abs_error_vs_y(), sim.sp[1]
+        want = sim.mean_abs_error_vs_y()
+        if oracle is not None:      # and the context entry point itself against the CPU oracle's serial sum
+            assert abs(want - oracle.mean_abs_error_vs_y(T)) < 1e-13
+        return want, sim.sp[1]
 
 
 def test_noalloc_matches_context_entry_point(h3, oracle):
@@ -38,7 +41,7 @@ def test_noalloc_matches_context_entry_point(h3, oracle):
     small = rng.random((9, 20, 33))
     for T in (big, small):            # the second field is smaller: slots used by the first call stay behind, stale
         nz, ny, nx = T.shape
-        want, sp_y = _expected(h3, T)
+        want, sp_y = _expected(h3, T, oracle)
         d_field = torch.from_numpy(T).to(dev)
         d_err = torch.full((1,), -1.0, dtype=torch.float64, device=dev)
         torch.cuda.synchronize()
@@ -49,6 +52,7 @@ def test_noalloc_matches_context_entry_point(h3, oracle):
             torch.cuda.synchronize()
             got = float(d_err.item())
             assert abs(got - want) < 1e-13, (call, got, want)
+            assert abs(got - oracle.mean_abs_error_vs_y(T)) < 1e-13, (call, got)
             if call == 1:             # by the second call the module is resident: no device memory may have been taken
                 assert torch.cuda.mem_get_info()[0] == free_before
     # pitched input: same field stored with padded rows

@@ -18,14 +18,17 @@ try:
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
 except Exception:
     pass
-TUNES = [t for t in os.environ.get("SWEEP_TUNES", "64,32,2,4,1;64,32,2,3,1;64,16,2,4,2;64,16,2,3,2;128,16,2,4,1;128,16,2,3,1;128,8,2,4,2").split(";")]
-CHUNKS = [int(c) for c in os.environ.get("SWEEP_CHUNKS", "16,32,64").split(",")]
+# a tune is "cx,cy,ry,stages,ctas" + the shared-memory access mode letter: L plain loads, S swapped x-neighbour loads,
+# P parity-split mid plane, X both (kernels_t2.cuh)
+TUNES = [t for t in os.environ.get("SWEEP_TUNES", "64,32,4,4,2P;64,32,4,4,2L;64,32,4,4,2X;64,16,2,4,3P;128,32,4,4,1P;64,64,4,4,1P").split(";")]
+# chunk length 0 = the guided plan (long chunks first, short ones last); > 0 = uniform chunks of that length
+CHUNKS = [int(c) for c in os.environ.get("SWEEP_CHUNKS", "0,64").split(",")]
 cells = (shape[0] - 2) * (shape[1] - 2) * (shape[2] - 2)
 for arith in ((0,) if os.environ.get("SWEEP_STRICT_ONLY") else (0, 1)):
     for tune in TUNES:
         for ch in CHUNKS:
-            base, sched = (tune[:-1], 1) if tune.endswith("L") else (tune[:-1], 2) if tune.endswith("P") else (tune, 0)
-            os.environ["HEAT3D_T2_TUNE"] = f"{base},{ch},{sched}"
+            base, xmode = tune[:-1], "LSPX".index(tune[-1])
+            os.environ["HEAT3D_T2_TUNE"] = f"{base},{ch},{xmode}"
             try:
                 with h3.Heat3D(*shape, arith=arith, temporal_k=2) as sim:
                     sim.init_reference_field()

@@ -251,6 +251,9 @@ def parity_preflight(h3, dist, torch, world, rank, local, arith, temporal_k, new
 
 def main():
     args = parse()
+    if os.environ.get("HEAT3D_BENCH_WATCHDOG_S"):      # diagnostics: dump every thread's stack and exit if the run overstays
+        import faulthandler
+        faulthandler.dump_traceback_later(float(os.environ["HEAT3D_BENCH_WATCHDOG_S"]), exit=True)
     if args.impl == "reference":
         return run_reference(args)
 

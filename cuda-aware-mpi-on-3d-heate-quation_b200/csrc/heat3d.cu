@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <array>
 #include <cfloat>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -18,6 +19,7 @@
 #include <dlfcn.h>
 #include <map>
 #include <new>
+#include <thread>
 #include <vector>
 
 namespace {
@@ -307,6 +309,36 @@ int set_dev(const Slab& s)
 {
     CU_TRY(cudaSetDevice(s.dev));
     return HEAT3D_OK;
+}
+
+// Multi-process contexts wait on flags another process writes (cuStreamWaitValue64 in the streams): if that process has
+// died the stream never drains and a plain cudaStreamSynchronize would hang with it.  These waits poll instead and
+// give up after HEAT3D_WATCHDOG_S seconds (default 900, 0 = wait for ever) with the sequence numbers needed to see
+// who is stuck.  Single-process contexts synchronise directly.
+int watched_sync(heat3d_ctx* c, Slab& s, cudaStream_t st, const char* what)
+{
+    static const double limit = getenv("HEAT3D_WATCHDOG_S") ? atof(getenv("HEAT3D_WATCHDOG_S")) : 900.0;
+    if (!c->multi_process || limit <= 0.0) {
+        CU_TRY(cudaStreamSynchronize(st));
+        return HEAT3D_OK;
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    unsigned spins = 0;
+    for (;;) {
+        const cudaError_t e = cudaStreamQuery(st);
+        if (e == cudaSuccess) return HEAT3D_OK;
+        if (e != cudaErrorNotReady) return fail(HEAT3D_ERR_CUDA, "cudaStreamQuery(%s) failed: %s", what, cudaGetErrorString(e));
+        if (++spins > 2000) std::this_thread::sleep_for(std::chrono::microseconds(50));      // busy-poll the first instants only
+        if ((spins & 1023u) == 0 && std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > limit) {
+            unsigned long long flags[4] = {0, 0, 0, 0};
+            cudaMemcpyAsync(flags, s.d_flags, sizeof flags, cudaMemcpyDeviceToHost, s.copy);     // a stream that is not stuck
+            cudaStreamSynchronize(s.copy);
+            return fail(HEAT3D_ERR_STATE,
+                        "slab %d: %s stream still busy after %.0f s - a neighbouring process has probably stopped.  Exchanges issued here: %llu; "
+                        "arrival flags from below/above: %llu/%llu; consumed flags: %llu/%llu",
+                        s.gidx, what, limit, c->seq, flags[0], flags[1], flags[2], flags[3]);
+        }
+    }
 }
 
 int make_tmap(Slab& s, CUtensorMap* map, int which, const heat3d_ctx* c, int box_x, int box_y)
@@ -822,7 +854,7 @@ int fetch_residual(heat3d_ctx* c, double* out)
             CU_TRY(cudaStreamWaitEvent(s.comm, s.ev_stop, 0));
             NCCL_TRY(g_nccl.AllReduce(s.d_res, s.d_scalar, 1, ncclFloat64, ncclMax, s.nccl, s.comm));
             CU_TRY(cudaMemcpyAsync(s.h_scalar, s.d_scalar, sizeof(double), cudaMemcpyDeviceToHost, s.comm));
-            CU_TRY(cudaStreamSynchronize(s.comm));
+            if ((rc = watched_sync(c, s, s.comm, "residual all-reduce"))) return rc;
         } else {
             CU_TRY(cudaMemcpyAsync(s.h_scalar, s.d_res, sizeof(double), cudaMemcpyDeviceToHost, s.compute));
             CU_TRY(cudaStreamSynchronize(s.compute));
@@ -843,6 +875,7 @@ int finish_timing(heat3d_ctx* c)
     for (Slab& s : c->slabs) {
         int rc = set_dev(s);
         if (rc) return rc;
+        if ((rc = watched_sync(c, s, s.compute, "compute"))) return rc;
         CU_TRY(cudaEventSynchronize(s.ev_stop));
         float ms = 0.f;
         CU_TRY(cudaEventElapsedTime(&ms, s.ev_start, s.ev_stop));
@@ -1044,11 +1077,10 @@ int mp_barrier(heat3d_ctx* c)
     Slab& s = c->slabs[0];
     int rc = set_dev(s);
     if (rc) return rc;
-    CU_TRY(cudaStreamSynchronize(s.compute));
-    CU_TRY(cudaStreamSynchronize(s.comm));
+    if ((rc = watched_sync(c, s, s.compute, "compute"))) return rc;
+    if ((rc = watched_sync(c, s, s.comm, "exchange"))) return rc;
     NCCL_TRY(g_nccl.AllReduce(s.d_scalar, s.d_scalar + 1, 1, ncclFloat64, ncclSum, s.nccl, s.comm));
-    CU_TRY(cudaStreamSynchronize(s.comm));
-    return HEAT3D_OK;
+    return watched_sync(c, s, s.comm, "barrier");
 }
 
 // compute + exchange streams only: snapshot (copy) and upload (h2d) transfers may keep running across this
@@ -1057,8 +1089,8 @@ int sync_compute(heat3d_ctx* c)
     for (Slab& s : c->slabs) {
         int rc = set_dev(s);
         if (rc) return rc;
-        CU_TRY(cudaStreamSynchronize(s.compute));
-        CU_TRY(cudaStreamSynchronize(s.comm));
+        if ((rc = watched_sync(c, s, s.compute, "compute"))) return rc;
+        if ((rc = watched_sync(c, s, s.comm, "exchange"))) return rc;
     }
     return HEAT3D_OK;
 }
@@ -1344,8 +1376,8 @@ int heat3d_sync(heat3d_ctx* c)
     if (rc) return rc;
     for (Slab& s : c->slabs) {
         if ((rc = set_dev(s))) return rc;
-        CU_TRY(cudaStreamSynchronize(s.compute));
-        CU_TRY(cudaStreamSynchronize(s.comm));
+        if ((rc = watched_sync(c, s, s.compute, "compute"))) return rc;
+        if ((rc = watched_sync(c, s, s.comm, "exchange"))) return rc;
         CU_TRY(cudaStreamSynchronize(s.copy));
         CU_TRY(cudaStreamSynchronize(s.h2d));
     }

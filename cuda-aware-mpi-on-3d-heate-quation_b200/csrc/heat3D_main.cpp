@@ -29,6 +29,8 @@
 //                          per-rank zones: the file equals the single-domain dump whatever P is)
 //   HEAT3D_TEMPORAL_K=1|2  updates fused per HBM pass (bit-identical results either way).  Default: 2 for grids of
 //                          2^25 points and more, where a pass is long against a host round trip, else 1
+//   HEAT3D_NSLABS_Y=Q      additionally cut the rows into Q ranges (2-D decomposition, Q x P sub-domains, HEAT3D_DEVICES then
+//                          lists Q*P ordinals): strided y-faces travel through pack / unpack kernels; depth 1 only
 //   HEAT3D_KERNEL=auto|tma|baseline
 //   HEAT3D_PERF=1          print GLUPS / algorithmic GB/s to stderr
 #include "../../include/heat3d.h"
@@ -323,11 +325,24 @@ int main(int argc, char** argv)
             devices.resize(ndev);
             for (unsigned i = 0; i < ndev; ++i) devices[i] = (int32_t)i;
         }
-        const unsigned ndev = (unsigned)devices.size();
-        p.nslabs = (int32_t)ndev; p.slab_first = 0; p.nlocal = (int32_t)ndev;
+        const unsigned qy = std::max(1u, env_unsigned("HEAT3D_NSLABS_Y", 1));
+        if (qy > 1) {
+            p.nslabs_y = (int32_t)qy;
+            p.temporal_k = 1;
+            if (devices.size() % qy != 0 || std::getenv("HEAT3D_DEVICES") == nullptr) {      // default: every sub-domain on its own GPU, wrapping around
+                int32_t have = 1;
+                H3(heat3d_device_count(&have));
+                devices.resize((size_t)qy * ndev);
+                for (size_t i = 0; i < devices.size(); ++i) devices[i] = (int32_t)(i % (size_t)std::max(1, have));
+            }
+        }
+        const unsigned pz = (unsigned)devices.size() / qy;
+        p.nslabs = (int32_t)pz; p.slab_first = 0; p.nlocal = (int32_t)pz;
     }
     p.devices = devices.data();
 
+    // stdout belongs to the reference's report: whatever NCCL wants to say (its version banner under NCCL_DEBUG) goes to stderr
+    if (world > 1) ::setenv("NCCL_DEBUG_FILE", "/dev/stderr", /*overwrite=*/0);
     heat3d_ctx* ctx = nullptr;
     H3(heat3d_create(&p, &ctx));
     if (world > 1 && root) ::unlink(idFile.c_str());        // every rank has read it: heat3d_create is collective

@@ -19,6 +19,7 @@
 #include <dlfcn.h>
 #include <map>
 #include <new>
+#include <string>
 #include <thread>
 #include <vector>
 
@@ -301,6 +302,22 @@ struct heat3d_ctx {
     unsigned long long consumed_seq = 0;   // depth-4 blocks issued so far: the value neighbours publish once they have read their ghosts
     bool timing_pending = false;       // a call's ev_start/ev_stop have not been folded into tm yet
     uint32_t call_steps = 0;           // steps issued by the current/last call
+    // ---- split along y (params.nslabs_y > 1): this context is then only a parent that owns one child context per
+    // y-range; each child is an ordinary context (z-slabs and all) over rows [y_off, y_off + p.ny) of the global field
+    int y_off = 0;                     // child: global row of local row 0
+    uint32_t ny_global = 0;            // child: rows of the global field (0 = not a child)
+    bool want_raw_error_sum = false;   // child: heat3d_mean_abs_error_vs_y returns the plain sum (the parent divides)
+    std::vector<heat3d_ctx*> kids;     // parent: children in order of y
+    struct YLink {                     // parent: one direction of one child-to-child face, per z-slab
+        int from_kid, to_kid, slab;
+        int src_row, dst_row;          // local row read in `from`, local ghost row written in `to`
+        double* stage_src = nullptr;   // dense (plane, x) buffer on the sender's device ...
+        double* stage_dst = nullptr;   // ... and on the receiver's (same pointer when both share a device)
+        cudaEvent_t ev_packed = nullptr, ev_unpacked = nullptr;
+    };
+    std::vector<YLink> ylinks;
+    cudaEvent_t g2_t0 = nullptr, g2_t1 = nullptr;   // parent: bracket of the last stepping call
+    std::string g2_exchange;           // parent: what heat3d_exchange_name answers
 };
 
 namespace {
@@ -1118,6 +1135,8 @@ int copy_planes(Slab& s, int b, uint32_t nx, uint32_t ny, uint32_t zl, uint32_t 
     return HEAT3D_OK;
 }
 
+#include "grid2d.inl"
+
 }  // namespace
 
 int h3::set_last_error(int code, const char* fmt, ...)
@@ -1164,6 +1183,10 @@ int heat3d_create(const heat3d_params* pin, heat3d_ctx** out)
     if (pin->struct_size != sizeof(heat3d_params))
         return fail(HEAT3D_ERR_INVALID, "heat3d_params.struct_size %u != %zu (header/library mismatch)", pin->struct_size, sizeof(heat3d_params));
     heat3d_params p = *pin;
+    if (p.nslabs_y > 1) {
+        if (p.nx < 3 || p.ny < 3 || p.nz < 3) return fail(HEAT3D_ERR_INVALID, "grid %ux%ux%u: every axis needs >= 3 points", p.nx, p.ny, p.nz);
+        return g2_create(p, out);
+    }
     if (p.nx < 3 || p.ny < 3 || p.nz < 3) return fail(HEAT3D_ERR_INVALID, "grid %ux%ux%u: every axis needs >= 3 points", p.nx, p.ny, p.nz);
     if (p.nx > (1u << 30) || p.ny > (1u << 30) || p.nz > (1u << 30)) return fail(HEAT3D_ERR_INVALID, "grid axis too large");
     if (p.arith != HEAT3D_ARITH_STRICT && p.arith != HEAT3D_ARITH_FMA) return fail(HEAT3D_ERR_INVALID, "unknown arith %d", p.arith);
@@ -1311,6 +1334,12 @@ int heat3d_create(const heat3d_params* pin, heat3d_ctx** out)
 int heat3d_destroy(heat3d_ctx* c)
 {
     if (!c) return HEAT3D_OK;
+    if (!c->kids.empty()) {
+        g2_sync(c);
+        g2_destroy(c);
+        delete c;
+        return HEAT3D_OK;
+    }
     for (Slab& s : c->slabs) {
         cudaSetDevice(s.dev);
         cudaDeviceSynchronize();
@@ -1333,6 +1362,7 @@ int heat3d_local_range(const heat3d_ctx* c, uint32_t* z0, uint32_t* z1)
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return heat3d_local_range(c->kids[0], z0, z1);
     if (z0) *z0 = c->slabs.front().z0;
     if (z1) *z1 = c->slabs.back().z1;
     return HEAT3D_OK;
@@ -1342,6 +1372,7 @@ int heat3d_layout(const heat3d_ctx* c, int32_t i, uint32_t* pitch, uint32_t* pla
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return heat3d_layout(c->kids[0], i, pitch, planes, ghost);
     if (i < 0 || i >= (int)c->slabs.size()) return fail(HEAT3D_ERR_INVALID, "local slab %d out of range", i);
     if (pitch) *pitch = c->slabs[i].pitch;
     if (planes) *planes = c->slabs[i].planes;
@@ -1352,6 +1383,7 @@ int heat3d_layout(const heat3d_ctx* c, int32_t i, uint32_t* pitch, uint32_t* pla
 const char* heat3d_kernel_name(const heat3d_ctx* c)
 {
     if (!c) return "";
+    if (!c->kids.empty()) return heat3d_kernel_name(c->kids[0]);
     if (c->variant2) return c->variant2->name;
     return c->use_tma ? c->variant->name : "baseline_64x4";
 }
@@ -1359,6 +1391,7 @@ const char* heat3d_kernel_name(const heat3d_ctx* c)
 const char* heat3d_exchange_name(const heat3d_ctx* c)
 {
     if (!c) return "";
+    if (!c->kids.empty()) return c->g2_exchange.c_str();
     if (c->store_mode) return "peer-store";
     if (c->multi_process) return c->slabs[0].ipc ? "ipc-put" : "nccl";
     return c->slabs.size() > 1 ? "peer-copy" : "none";
@@ -1366,7 +1399,7 @@ const char* heat3d_exchange_name(const heat3d_ctx* c)
 
 void* heat3d_compute_stream(heat3d_ctx* c, int32_t i)
 {
-    if (!c || i < 0 || i >= (int)c->slabs.size()) return nullptr;
+    if (!c || i < 0 || i >= (int)c->slabs.size()) return nullptr;      // (a parent of a y split has no slabs of its own)
     return (void*)c->slabs[i].compute;
 }
 
@@ -1374,6 +1407,7 @@ int heat3d_sync(heat3d_ctx* c)
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return g2_sync(c);
     for (Slab& s : c->slabs) {
         if ((rc = set_dev(s))) return rc;
         if ((rc = watched_sync(c, s, s.compute, "compute"))) return rc;
@@ -1388,12 +1422,13 @@ int heat3d_init_reference_field(heat3d_ctx* c, double sp_y)
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return g2_init(c, sp_y);
     if ((rc = heat3d_sync(c))) return rc;
     if ((rc = mp_barrier(c))) return rc;      // no neighbour may still be writing into the ghosts this call rewrites
     for (Slab& s : c->slabs) {
         if ((rc = set_dev(s))) return rc;
         h3::init_reference_field_kernel<<<s.num_sms * 8, 256, 0, s.compute>>>(s.buf[0], s.buf[1], (int)c->p.nx, (int)c->p.ny, (int)s.pitch,
-                                                                             (int)s.planes, s.zg0, (int)c->p.nz, sp_y);
+                                                                             (int)s.planes, s.zg0, (int)c->p.nz, sp_y, c->y_off, c->ny_global ? (int)c->ny_global : (int)c->p.ny);
         CU_TRY(cudaGetLastError());
         c->tm.launches++;
         // ghosts are filled by the formula itself, so the first step has nothing to wait for
@@ -1411,6 +1446,7 @@ int heat3d_upload_planes(heat3d_ctx* c, const double* host, uint32_t z0, uint32_
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return host ? g2_transfer(c, const_cast<double*>(host), z0, n, true) : fail(HEAT3D_ERR_INVALID, "null host pointer");
     if (!host) return fail(HEAT3D_ERR_INVALID, "null host pointer");
     if (z0 < c->slabs.front().z0 || z0 + n > c->slabs.back().z1)
         return fail(HEAT3D_ERR_INVALID, "planes [%u,%u) outside this context's range [%u,%u)", z0, z0 + n, c->slabs.front().z0, c->slabs.back().z1);
@@ -1443,6 +1479,7 @@ int heat3d_upload_planes_async(heat3d_ctx* c, const double* host, uint32_t z0, u
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return g2_fail_unsupported("heat3d_upload_planes_async");
     if (!host) return fail(HEAT3D_ERR_INVALID, "null host pointer");
     if (z0 < c->slabs.front().z0 || z0 + n > c->slabs.back().z1)
         return fail(HEAT3D_ERR_INVALID, "planes [%u,%u) outside this context's range [%u,%u)", z0, z0 + n, c->slabs.front().z0, c->slabs.back().z1);
@@ -1478,6 +1515,7 @@ int heat3d_upload_commit(heat3d_ctx* c)
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return g2_fail_unsupported("heat3d_upload_commit");
     bool any = false;
     for (Slab& s : c->slabs) any = any || s.up_b > s.up_a;
     if (!any) return fail(HEAT3D_ERR_STATE, "heat3d_upload_commit without a staged heat3d_upload_planes_async");
@@ -1509,6 +1547,7 @@ int heat3d_upload(heat3d_ctx* c, const double* host_global)
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return host_global ? g2_transfer(c, const_cast<double*>(host_global), 0, c->p.nz, true) : fail(HEAT3D_ERR_INVALID, "null host pointer");
     if (!host_global) return fail(HEAT3D_ERR_INVALID, "null host pointer");
     const uint32_t z0 = c->slabs.front().z0, z1 = c->slabs.back().z1;
     return heat3d_upload_planes(c, host_global + (size_t)z0 * c->p.nx * c->p.ny, z0, z1 - z0);
@@ -1518,6 +1557,7 @@ int heat3d_download_planes(heat3d_ctx* c, double* host, uint32_t z0, uint32_t n)
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return host ? g2_transfer(c, host, z0, n, false) : fail(HEAT3D_ERR_INVALID, "null host pointer");
     if (!host) return fail(HEAT3D_ERR_INVALID, "null host pointer");
     if (z0 < c->slabs.front().z0 || z0 + n > c->slabs.back().z1)
         return fail(HEAT3D_ERR_INVALID, "planes [%u,%u) outside this context's range [%u,%u)", z0, z0 + n, c->slabs.front().z0, c->slabs.back().z1);
@@ -1535,6 +1575,7 @@ int heat3d_download(heat3d_ctx* c, double* host_global)
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return host_global ? g2_transfer(c, host_global, 0, c->p.nz, false) : fail(HEAT3D_ERR_INVALID, "null host pointer");
     if (!host_global) return fail(HEAT3D_ERR_INVALID, "null host pointer");
     const uint32_t z0 = c->slabs.front().z0, z1 = c->slabs.back().z1;
     return heat3d_download_planes(c, host_global + (size_t)z0 * c->p.nx * c->p.ny, z0, z1 - z0);
@@ -1604,6 +1645,7 @@ int heat3d_step(heat3d_ctx* c, uint32_t nsteps)
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return g2_step(c, nsteps, nullptr);
     if ((rc = begin_call(c))) return rc;
     if ((rc = advance_plain(c, nsteps))) return rc;
     if (nsteps) c->have_res = false;
@@ -1614,6 +1656,13 @@ int heat3d_step_residual(heat3d_ctx* c, uint32_t nsteps, double* residual)
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) {
+        if (!residual || nsteps == 0) return fail(HEAT3D_ERR_INVALID, "heat3d_step_residual needs a residual pointer and nsteps >= 1");
+        if ((rc = g2_step(c, nsteps, residual))) return rc;
+        if (*residual < DBL_MIN) *residual = DBL_MIN;     // cu:1019
+        c->last_res = *residual;
+        return HEAT3D_OK;
+    }
     if (!residual) return fail(HEAT3D_ERR_INVALID, "null residual pointer");
     if (nsteps == 0) return fail(HEAT3D_ERR_INVALID, "nsteps must be >= 1 to produce a residual");
     if ((rc = begin_call(c))) return rc;
@@ -1784,7 +1833,7 @@ int heat3d_run(heat3d_ctx* c, uint32_t iter_max, double eps, uint32_t check_ever
     uint32_t fin = 0, done = 0;
     int32_t conv = 0;
     uint32_t time = 0;
-    if (check_every == 1 && !c->multi_process && c->snap_buf < 0) {
+    if (check_every == 1 && !c->multi_process && c->snap_buf < 0 && c->kids.empty()) {
         if ((rc = c->variant2 ? run_every_iteration_t2(c, iter_max, eps, &fin, &conv, &done)
                               : run_every_iteration(c, iter_max, eps, &fin, &conv, &done))) return rc;
         time = iter_max;
@@ -1811,13 +1860,14 @@ int heat3d_mean_abs_error_vs_y(heat3d_ctx* c, double sp_y, double* err)
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return err ? g2_error(c, sp_y, err) : fail(HEAT3D_ERR_INVALID, "null output pointer");
     if (!err) return fail(HEAT3D_ERR_INVALID, "null output pointer");
     double sum = 0.0;
     for (Slab& s : c->slabs) {
         if ((rc = set_dev(s))) return rc;
         if (s.zb > s.za) {
             h3::abs_error_partial_kernel<<<s.partial_blocks, 256, 0, s.compute>>>(s.buf[c->cur], (int)c->p.nx, (int)c->p.ny, (int)s.pitch,
-                                                                                  s.plane, s.za, s.zb, sp_y, s.d_partial);
+                                                                                  s.plane, s.za, s.zb, sp_y, s.d_partial, c->y_off);
             CU_TRY(cudaGetLastError());
             h3::sum_partials_kernel<<<1, 256, 0, s.compute>>>(s.d_partial, s.partial_blocks, s.d_scalar);
             CU_TRY(cudaGetLastError());
@@ -1840,7 +1890,7 @@ int heat3d_mean_abs_error_vs_y(heat3d_ctx* c, double sp_y, double* err)
     }
     // the reference divides by an `unsigned` product (cu:1102); keep its wrap-around for grids beyond 2^32 cells
     const unsigned denom = (c->p.nx - 2u) * (c->p.ny - 2u) * (c->p.nz - 2u);
-    *err = sum / denom;
+    *err = c->want_raw_error_sum ? sum : sum / denom;
     return HEAT3D_OK;
 }
 
@@ -1848,6 +1898,7 @@ int heat3d_snapshot_async(heat3d_ctx* c, double* pinned)
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return g2_fail_unsupported("heat3d_snapshot_async");
     if (!pinned) return fail(HEAT3D_ERR_INVALID, "null host pointer");
     if ((rc = heat3d_snapshot_wait(c))) return rc;           // one snapshot in flight at a time
     const size_t plane_host = (size_t)c->p.nx * c->p.ny;
@@ -1889,6 +1940,7 @@ int heat3d_snapshot_strided_async(heat3d_ctx* c, double* pinned, uint32_t sx, ui
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return g2_fail_unsupported("heat3d_snapshot_strided_async");
     if (!pinned) return fail(HEAT3D_ERR_INVALID, "null host pointer");
     if (sx == 0 || sy == 0 || sz == 0) return fail(HEAT3D_ERR_INVALID, "strides must be >= 1");
     if (sx == 1 && sy == 1 && sz == 1) return heat3d_snapshot_async(c, pinned);
@@ -1940,6 +1992,7 @@ int heat3d_snapshot_wait(heat3d_ctx* c)
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) return HEAT3D_OK;
     for (Slab& s : c->slabs) {
         if ((rc = set_dev(s))) return rc;
         CU_TRY(cudaStreamSynchronize(s.copy));
@@ -1966,6 +2019,12 @@ int heat3d_get_timing(heat3d_ctx* c, heat3d_timing* t)
 {
     int rc = check_ctx(c);
     if (rc) return rc;
+    if (!c->kids.empty()) {
+        if (!t) return fail(HEAT3D_ERR_INVALID, "null output");
+        if ((rc = g2_finish_timing(c))) return rc;
+        *t = c->tm;
+        return HEAT3D_OK;
+    }
     if (!t) return fail(HEAT3D_ERR_INVALID, "null output");
     if ((rc = finish_timing(c))) return rc;
     *t = c->tm;

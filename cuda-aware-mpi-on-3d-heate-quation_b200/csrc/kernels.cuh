@@ -123,12 +123,13 @@ __device__ __forceinline__ void cta_residual_commit(double r, unsigned long long
 // Order of the reference's writes: zero; y-top plane = 1.0; then x=0 / x=nx-1 / z=0 / z=nz-1 faces =
 // j*sp_y — so the four side faces win on the top edges.
 // ------------------------------------------------------------------------------------------------------
+// (y_off / ny_global: a sub-box of a y-split holds rows [y_off, y_off + ny) of a field with ny_global rows; 0 / ny otherwise)
 __global__ void init_reference_field_kernel(double* __restrict__ a, double* __restrict__ b, int nx, int ny, int pitch,
-                                            int planes, long long zg0, int nz_global, double sp_y)
+                                            int planes, long long zg0, int nz_global, double sp_y, int y_off, int ny_global)
 {
     const long long rows = (long long)ny * planes;
     for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
-        const int zl = (int)(row / ny), j = (int)(row % ny);
+        const int zl = (int)(row / ny), jl = (int)(row % ny), j = jl + y_off;
         const long long zg = zg0 + zl;
         const bool in_domain = zg >= 0 && zg < nz_global;
         const bool zface = zg == 0 || zg == nz_global - 1;
@@ -137,7 +138,7 @@ __global__ void init_reference_field_kernel(double* __restrict__ a, double* __re
         for (int i = threadIdx.x; i < pitch; i += blockDim.x) {
             double v = 0.0;
             if (in_domain && i < nx) {
-                if (j == ny - 1) v = 1.0;
+                if (j == ny_global - 1) v = 1.0;
                 if (i == 0 || i == nx - 1 || zface) v = (double)j * sp_y;
             }
             ra[i] = v;
@@ -548,6 +549,35 @@ __global__ void __launch_bounds__((TX / 2) * (TY / RY), MINB)
 }
 
 // ------------------------------------------------------------------------------------------------------
+// K3: pack / unpack of a strided face.  Under a split along y a face is `nrows` rows of every owned plane: nx doubles
+// contiguous, then a jump of a whole plane (the reference gathers its Y faces the same way, element by element on the
+// host, heat3D.cu:576-589).  pack gathers rows [row0, row0 + nrows) of planes [z0, z0 + nplanes) into a dense buffer
+// ordered (plane, row, x); unpack scatters such a buffer into the ghost rows of the receiving sub-box.  One block per
+// (row, plane); 128-bit accesses when nx is even (rows start 128-byte aligned: the pitch is a multiple of 16 doubles).
+// ------------------------------------------------------------------------------------------------------
+template <bool PACK>
+__global__ void __launch_bounds__(256) face_rows_kernel(double* __restrict__ field, double* __restrict__ buf, int nx, int nrows, int row0,
+                                                        int z0, int pitch, long long plane)
+{
+    const int r = blockIdx.x, p = blockIdx.y;
+    double* frow = field + (long long)(z0 + p) * plane + (long long)(row0 + r) * pitch;
+    double* brow = buf + ((long long)p * nrows + r) * nx;
+    if ((nx & 1) == 0) {
+        double2* f2 = (double2*)frow;
+        double2* b2 = (double2*)brow;
+        for (int i = threadIdx.x; i < nx / 2; i += 256) {
+            if (PACK) b2[i] = f2[i];
+            else f2[i] = b2[i];
+        }
+    } else {
+        for (int i = threadIdx.x; i < nx; i += 256) {
+            if (PACK) brow[i] = frow[i];
+            else frow[i] = brow[i];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
 // Decimated snapshot: every sx-th / sy-th point of every listed plane, packed densely (x fastest) for the trip over
 // PCIe.  Plane p of the output is local plane zl0 + p*sz of the field.  One block per (output row, output plane).
 // ------------------------------------------------------------------------------------------------------
@@ -585,13 +615,13 @@ __device__ __forceinline__ double block_sum(double v)
 // rows = (ny-2) * number of owned interior planes; row r -> plane za + r/(ny-2), y = 1 + r%(ny-2).
 __global__ void __launch_bounds__(256) abs_error_partial_kernel(const double* __restrict__ f, int nx, int ny, int pitch,
                                                                 long long plane, int za, int zb, double sp_y,
-                                                                double* __restrict__ partial)
+                                                                double* __restrict__ partial, int y_off)
 {
     const long long rows = (long long)(ny - 2) * (zb - za);
     double acc = 0.0;
     for (long long row = blockIdx.x; row < rows; row += gridDim.x) {
         const int z = za + (int)(row / (ny - 2)), j = 1 + (int)(row % (ny - 2));
-        const double yj = (double)j * sp_y;
+        const double yj = (double)(j + y_off) * sp_y;
         const double* p = f + (long long)z * plane + (long long)j * pitch;
         for (int i = 1 + threadIdx.x; i <= nx - 2; i += 256) acc += fabs(__dsub_rn(p[i], yj));
     }

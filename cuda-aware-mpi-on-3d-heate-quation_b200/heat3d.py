@@ -33,7 +33,7 @@ class Params(C.Structure):
                 ("arith", C.c_int32), ("temporal_k", C.c_int32), ("kernel", C.c_int32),
                 ("nslabs", C.c_int32), ("slab_first", C.c_int32), ("nlocal", C.c_int32),
                 ("devices", C.POINTER(C.c_int32)), ("nccl_unique_id", C.c_void_p), ("stream", C.c_void_p),
-                ("flags", C.c_uint32), ("tune", C.c_int32 * 6)]
+                ("flags", C.c_uint32), ("tune", C.c_int32 * 6), ("nslabs_y", C.c_int32)]
 
 
 class Timing(C.Structure):
@@ -153,7 +153,7 @@ class Heat3D:
     """One heat3d_ctx.  Fields cross the boundary as float64 arrays of shape (nz, ny, nx), x fastest."""
 
     def __init__(self, nx, ny, nz, D=None, arith=ARITH_STRICT, kernel=KERNEL_AUTO, temporal_k=1, nslabs=1,
-                 slab_first=0, nlocal=0, devices=None, nccl_id=None, stream=None, flags=0, tune=None):
+                 slab_first=0, nlocal=0, devices=None, nccl_id=None, stream=None, flags=0, tune=None, nslabs_y=0):
         L = lib()
         self.nx, self.ny, self.nz = nx, ny, nz
         self.sp, self.dt, Dref = coefficients(nx, ny, nz)
@@ -175,6 +175,7 @@ class Heat3D:
         if stream is not None:
             p.stream = stream
         p.flags = flags
+        p.nslabs_y = nslabs_y
         if tune:
             for i, v in enumerate(tune):
                 p.tune[i] = v

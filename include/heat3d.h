@@ -82,6 +82,14 @@ typedef struct heat3d_params {
     uint32_t flags;             /* HEAT3D_FLAG_*                                                           */
     int32_t tune[6];            /* kernel tuning overrides (0 = default): tile_x, tile_y, rows_per_thread,
                                    stages, ctas_per_sm, chunk_len                                         */
+    int32_t nslabs_y;           /* 0/1 = z-slabs only.  > 1: 2-D decomposition, nslabs_y ranges of rows times nslabs
+                                   z-slabs (the reference cuts all three axes, cu:243-263, 385-389); faces between row
+                                   ranges are strided in memory and travel through pack / unpack kernels (the reference's
+                                   host-side face packing, cu:562-605).  One process only, temporal_k = 1; `devices` then
+                                   holds nslabs_y * nslabs ordinals, index iy * nslabs + iz.  Ownership is non-overlapping
+                                   with one ghost row per side, so the field equals the single-domain result bit for bit -
+                                   the reference's shared-interface scheme with extrapolated edges and averaged corners
+                                   (cu:861-1011) is deliberately not reproduced (out of scope)            */
 } heat3d_params;
 
 #define HEAT3D_FLAG_NO_OVERLAP 0x1u /* serialise halo exchange after compute (for exposed-halo measurement) */

@@ -171,3 +171,12 @@ def test_driver_one_process_per_slab(h3, manifest, tmp_path, world):
         assert all(o[0] == "" for o in outs[1:])               # only rank 0 talks
         assert sorted(os.listdir(wd / "output")) == ["out.dat"]
         assert hashlib.md5(open(wd / "output" / "out.dat", "rb").read()).hexdigest() == m["dump_md5"]
+
+
+def test_driver_2d_decomposition_same_output(h3, manifest, tmp_path):
+    """HEAT3D_NSLABS_Y: rows cut into ranges on top of the z-slabs; report and dump stay the single-domain ones."""
+    m = manifest["aniso_33x17x65"]
+    r = _run(h3, m["args"], str(tmp_path), {"HEAT3D_NSLABS_Y": "2", "HEAT3D_DEVICES": "0,0,0,0"})
+    assert r.returncode == 0, r.stderr
+    assert _report(r.stdout) == m["stdout"]
+    assert hashlib.md5(open(tmp_path / "output" / "out.dat", "rb").read()).hexdigest() == m["dump_md5"]

@@ -283,3 +283,44 @@ def test_long_runs_through_cuda_graphs(h3, oracle, k):
         sim.step(1)                                    # buffer parity flipped: the other graph gets built next
         sim.step(32 * k)
         assert np.array_equal(sim.download(), _oracle_field(oracle, nx, ny, nz, nsteps + 1 + 32 * k))
+
+
+@pytest.mark.parametrize("shape,py,pz,nsteps", [((40, 24, 31), 2, 1, 20), ((45, 31, 22), 3, 2, 17), ((130, 35, 29), 2, 3, 12), ((33, 64, 16), 4, 2, 9),
+                                                ((150, 70, 40), 5, 1, 11)])
+def test_2d_decomposition_equals_single_domain_bitwise(h3, oracle, shape, py, pz, nsteps):
+    """nslabs_y > 1: ranges of rows times z-slabs.  The faces between row ranges are strided in memory and travel through
+    the pack / unpack kernels (the reference's host-side face packing, heat3D.cu:562-605); ownership is non-overlapping,
+    so field, residual, error norm, uploads and the convergence loop must be the single domain's, bit for bit."""
+    nx, ny, nz = shape
+    _, _, D = oracle.coefficients(nx, ny, nz)
+    ref = _oracle_field(oracle, nx, ny, nz, nsteps)
+    prev = _oracle_field(oracle, nx, ny, nz, nsteps - 1)
+    with h3.Heat3D(nx, ny, nz, nslabs=pz, nslabs_y=py, devices=[0] * (py * pz)) as sim:
+        assert sim.exchange_name().startswith("y: pack/unpack")
+        sim.init_reference_field()
+        assert np.array_equal(sim.download(), oracle.init_field(nx, ny, nz))
+        sim.step(nsteps - 1)
+        res = sim.step_residual(1)
+        got = sim.download()
+        assert np.array_equal(got, ref)
+        assert res == oracle.residual(ref, prev)
+        assert abs(sim.mean_abs_error_vs_y() - oracle.mean_abs_error_vs_y(ref)) < 1e-13
+        t = sim.timing()
+        assert t["steps"] == nsteps and t["last_call_ms"] > 0
+        T = np.random.default_rng(12).random((nz, ny, nx))
+        sim.upload(T)
+        assert np.array_equal(sim.download(), T)
+        sim.step(6)
+        assert np.array_equal(sim.download(), oracle.steps(T.copy(), D, 6))
+        assert np.array_equal(sim.download_planes(3, 5), oracle.steps(T.copy(), D, 6)[3:8])
+    with pytest.raises(h3.Heat3DError):
+        h3.Heat3D(nx, ny, nz, nslabs_y=2, temporal_k=2, devices=[0, 0])
+
+
+def test_2d_decomposition_convergence_run_matches_reference_program(h3, manifest, golden_field):
+    nx, ny, nz, it, eps = manifest["c27_converge"]["args"]
+    with h3.Heat3D(nx, ny, nz, nslabs=2, nslabs_y=3, devices=[0] * 6) as sim:
+        sim.init_reference_field()
+        applied, fin, conv = sim.run(it, float(eps), check_every=1)
+        assert (applied, fin, conv) == (3303, 3302, True)
+        assert np.array_equal(sim.download(), golden_field("c27_converge"))

@@ -341,10 +341,25 @@ int main(int argc, char** argv)
     }
     p.devices = devices.data();
 
-    // stdout belongs to the reference's report: whatever NCCL wants to say (its version banner under NCCL_DEBUG) goes to stderr
-    if (world > 1) ::setenv("NCCL_DEBUG_FILE", "/dev/stderr", /*overwrite=*/0);
+    // stdout belongs to the reference's report: NCCL prints its version banner there while the communicator comes up
+    // (under NCCL_DEBUG=VERSION and louder), so for that one call file descriptor 1 points at stderr
     heat3d_ctx* ctx = nullptr;
-    H3(heat3d_create(&p, &ctx));
+    {
+        int saved = -1;
+        if (world > 1) {
+            std::cout.flush();
+            std::fflush(stdout);
+            saved = ::dup(1);
+            if (saved >= 0) ::dup2(2, 1);
+        }
+        const int rc = heat3d_create(&p, &ctx);
+        if (saved >= 0) {
+            std::fflush(stdout);
+            ::dup2(saved, 1);
+            ::close(saved);
+        }
+        if (rc != HEAT3D_OK) die("heat3d_create(&p, &ctx)");
+    }
     if (world > 1 && root) ::unlink(idFile.c_str());        // every rank has read it: heat3d_create is collective
     H3(heat3d_init_reference_field(ctx, spacing[1]));     // cu:409-453
 

@@ -304,7 +304,8 @@ def test_2d_decomposition_equals_single_domain_bitwise(h3, oracle, shape, py, pz
         got = sim.download()
         assert np.array_equal(got, ref)
         assert res == oracle.residual(ref, prev)
-        assert abs(sim.mean_abs_error_vs_y() - oracle.mean_abs_error_vs_y(ref)) < 1e-13
+        want_err = oracle.mean_abs_error_vs_y(ref)       # serial sum there, per-range tree sums here: relative 1e-12
+        assert abs(sim.mean_abs_error_vs_y() - want_err) < 1e-12 * want_err
         t = sim.timing()
         assert t["steps"] == nsteps and t["last_call_ms"] > 0
         T = np.random.default_rng(12).random((nz, ny, nx))

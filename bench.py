@@ -53,6 +53,8 @@ def parse():
     ap.add_argument("--grid", default="", help="nx,ny,nz: explicit global grid (experiments; overrides --workload)")
     ap.add_argument("--snapshot-every", type=int, default=0,
                     help="async snapshot of the field to pinned host memory every M bench steps inside the timed loop")
+    ap.add_argument("--snapshot-stride", type=int, default=1,
+                    help="with --snapshot-every: keep every s-th point per axis (decimated on the GPU before the copy)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-preflight", action="store_true", help="N>1: skip the bitwise parity pre-flight")
@@ -336,11 +338,16 @@ def main():
 
     # ---------------- device-resident throughput ----------------
     sim.init_reference_field()
-    snap_buf, nsnap = (h3.pinned_empty((z1 - z0, ny, nx)), [0]) if args.snapshot_every else (None, [0])
+    ss = max(1, args.snapshot_stride)
+    snap_shape = (z1 - z0, ny, nx) if ss == 1 else sim.strided_local_shape(ss, ss, ss)
+    snap_buf, nsnap = (h3.pinned_empty(snap_shape), [0]) if args.snapshot_every else (None, [0])
 
     def snapshot(it):
         if snap_buf is not None and it % args.snapshot_every == 0:
-            sim.snapshot_async_local(snap_buf)      # D2H on the copy stream while the next updates run
+            if ss == 1:
+                sim.snapshot_async_local(snap_buf)      # D2H on the copy stream while the next updates run
+            else:
+                sim.snapshot_strided_async_local(snap_buf, ss, ss, ss)
             nsnap[0] += 1
 
     sampler = ClockSampler(local)
@@ -504,7 +511,8 @@ def main():
                            "l2": "inputs exceed L2 (two %.1f GiB buffers per GPU vs 126 MB)" % ((z1 - z0) * ny * nx * 8 / 2**30)},
                 "roofline": roofline, "roofline_k1": roofline_k1, "arith_fma": arith_fma, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
                 "parity_preflight": preflight, "scaling_base_glups": scaling_base, "parallel_efficiency": parallel_eff, "strong_1024": strong,
-                "wall_ms_per_step": wall_ms / args.steps, "snapshots": {"count": nsnap, "bytes_each_per_rank": int(snap_buf.nbytes)} if snap_buf is not None else None,
+                "wall_ms_per_step": wall_ms / args.steps, "snapshots": {"count": nsnap, "bytes_each_per_rank": int(snap_buf.nbytes), "stride": ss, "every_steps": args.snapshot_every,
+                              "headline": "wall_glups_incl_snapshots"} if snap_buf is not None else None,
                 "wall_glups_incl_snapshots": total_updates / (wall_ms * 1e-3) / 1e9, "exposed_halo_ms_per_update": halo_ms / (tsteps * args.steps) if n > 1 else None,
                 "exposed_halo_ms_per_update_min_rank": halo_ms_min / (tsteps * args.steps) if n > 1 else None,
                 "exchange": sim.exchange_name(),

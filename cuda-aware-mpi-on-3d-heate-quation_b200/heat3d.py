@@ -279,6 +279,22 @@ class Heat3D:
         assert pinned.dtype == np.float64 and pinned.flags["C_CONTIGUOUS"] and pinned.shape == shape, (pinned.shape, shape)
         _check(lib().heat3d_snapshot_strided_async(self._ctx, pinned.ctypes.data_as(_dp), sx, sy, sz))
 
+    def strided_local_shape(self, sx, sy, sz):
+        """Shape of the decimated array holding only THIS context's planes."""
+        z0, z1 = self.local_range()
+        first = -(-z0 // sz) * sz
+        return (max(0, -(-(z1 - first) // sz)) if first < z1 else 0, -(-self.ny // sy), -(-self.nx // sx))
+
+    def snapshot_strided_async_local(self, pinned_local, sx, sy, sz):
+        """As snapshot_strided_async for a pinned array of strided_local_shape(): the C entry point addresses decimated
+        planes by their global index, so it is handed the address decimated plane 0 would have."""
+        shape = self.strided_local_shape(sx, sy, sz)
+        assert pinned_local.dtype == np.float64 and pinned_local.flags["C_CONTIGUOUS"] and pinned_local.shape == shape, (pinned_local.shape, shape)
+        z0, _ = self.local_range()
+        first_k = -(-z0 // sz)
+        base = pinned_local.ctypes.data - first_k * shape[1] * shape[2] * 8
+        _check(lib().heat3d_snapshot_strided_async(self._ctx, C.cast(C.c_void_p(base), _dp), sx, sy, sz))
+
     def snapshot_wait(self):
         _check(lib().heat3d_snapshot_wait(self._ctx))
 

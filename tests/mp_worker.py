@@ -58,6 +58,42 @@ def main():
         t = torch.tensor([local], dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         assert max(t.item(), np.finfo(np.float64).tiny) == oracle.residual(ref, ref_prev)
+        # ghost depth 4 (temporal_k = 4): blocks of four updates with ONE exchange of four planes per side.  Update j of a
+        # block covers the owned planes plus 4-j ghost planes on every side that has a neighbour - the schedule of the
+        # library's step_block4 (pass A = updates 1-2 ending two ghost planes deep, pass B = updates 3-4) - and the tail of
+        # nsteps % 4 updates exchanges after every update.
+        if all(b - a >= 4 for a, b in h3.slab_bounds(nz, world)):
+            G = 4
+            cur = oracle.init_field(nx, ny, nz)
+            nxt = cur.copy()
+
+            def exchange(buf, depth):
+                reqs = []
+                if rank > 0:
+                    reqs.append(dist.isend(torch.from_numpy(buf[z0:z0 + depth]), rank - 1))
+                    reqs.append(dist.irecv(torch.from_numpy(buf[z0 - depth:z0]), rank - 1))
+                if rank < world - 1:
+                    reqs.append(dist.isend(torch.from_numpy(buf[z1 - depth:z1]), rank + 1))
+                    reqs.append(dist.irecv(torch.from_numpy(buf[z1:z1 + depth]), rank + 1))
+                for r in reqs:
+                    r.wait()
+
+            done = 0
+            while nsteps - done >= 4:
+                for j in range(1, 5):
+                    ext = G - j
+                    oracle.step_planes(cur, nxt, D, z0 - ext if rank > 0 else z0, z1 + ext if rank < world - 1 else z1)
+                    cur, nxt = nxt, cur
+                exchange(cur, G)
+                nxt[max(z0 - G, 0):min(z1 + G, nz)] = cur[max(z0 - G, 0):min(z1 + G, nz)]      # both buffers carry the Dirichlet shell
+                done += 4
+            while done < nsteps:
+                oracle.step_planes(cur, nxt, D, z0, z1)
+                exchange(nxt, G)
+                cur, nxt = nxt, cur
+                done += 1
+            lo4, hi4 = max(z0 - G, 0), min(z1 + G, nz)
+            assert np.array_equal(cur[lo4:hi4], ref[lo4:hi4]), f"rank {rank}: ghost-depth-4 slab differs from single domain"
     else:
         local = int(os.environ.get("LOCAL_RANK", rank))
         torch.cuda.set_device(local)

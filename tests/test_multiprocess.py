@@ -25,7 +25,7 @@ def _launch(world, backend, shape_steps, timeout=300):
         assert f"rank {k}/{world} {backend} ok" in r.stdout
 
 
-@pytest.mark.parametrize("world,shape_steps", [(2, (21, 13, 30, 12)), (3, (16, 9, 11, 7))])
+@pytest.mark.parametrize("world,shape_steps", [(2, (21, 13, 30, 12)), (3, (16, 9, 11, 7)), (3, (16, 9, 17, 11))])
 def test_gloo_slabs_equal_single_domain(world, shape_steps):
     _launch(world, "gloo", shape_steps)
 

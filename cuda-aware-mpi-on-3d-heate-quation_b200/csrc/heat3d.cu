@@ -1005,8 +1005,8 @@ int setup_slab(heat3d_ctx* c, Slab& s)
     CU_TRY(cudaMemset(s.d_res_base, 0, 3 * sizeof(unsigned long long)));
     s.partial_blocks = s.num_sms * 8;
     CU_TRY(cudaMalloc(&s.d_partial, (size_t)s.partial_blocks * sizeof(double)));
-    CU_TRY(cudaMalloc(&s.d_scalar, 2 * sizeof(double)));
-    CU_TRY(cudaHostAlloc(&s.h_scalar, 4 * sizeof(double), cudaHostAllocDefault));   // [0..1] queries, [2..3] pipelined residuals
+    CU_TRY(cudaMalloc(&s.d_scalar, 8 * sizeof(double)));                // [0..1] reductions, [4..6] all-reduced residual slots
+    CU_TRY(cudaHostAlloc(&s.h_scalar, 8 * sizeof(double), cudaHostAllocDefault));   // [0..1] queries, [2..3] pipelined residuals, [4..6] all-reduced slots
     // local output range: owned planes that are global interior planes
     long long a = (long long)s.G, b = (long long)s.G + (s.z1 - s.z0);
     const long long lo = 1 - s.zg0, hi = (long long)p.nz - 1 - s.zg0;
@@ -1777,6 +1777,18 @@ static int run_every_iteration_t2(heat3d_ctx* c, uint32_t iter_max, double eps, 
         for (Slab& s : c->slabs) {
             int r0 = set_dev(s);
             if (r0) return r0;
+            if (c->multi_process) {
+                // one all-reduce (max; bit patterns of non-negative doubles order like the doubles) brings every process the
+                // residuals of BOTH updates: all of them then take the same decision, one host round trip per two iterations
+                CU_TRY(cudaEventRecord(s.ev_tmp, s.compute));
+                CU_TRY(cudaStreamWaitEvent(s.comm, s.ev_tmp, 0));
+                NCCL_TRY(g_nccl.AllReduce(s.d_res_base, s.d_scalar + 4, 3, ncclFloat64, ncclMax, s.nccl, s.comm));
+                CU_TRY(cudaMemcpyAsync(s.h_scalar + 4, s.d_scalar + 4, 3 * sizeof(double), cudaMemcpyDeviceToHost, s.comm));
+                if ((r0 = watched_sync(c, s, s.comm, "residual all-reduce"))) return r0;
+                second = s.h_scalar[4];
+                first = s.h_scalar[6];
+                break;
+            }
             CU_TRY(cudaMemcpyAsync(s.h_scalar + 2, s.d_res_base, sizeof(double), cudaMemcpyDeviceToHost, s.compute));
             CU_TRY(cudaMemcpyAsync(s.h_scalar + 3, s.d_res_base + 2, sizeof(double), cudaMemcpyDeviceToHost, s.compute));
             CU_TRY(cudaStreamSynchronize(s.compute));
@@ -1833,7 +1845,8 @@ int heat3d_run(heat3d_ctx* c, uint32_t iter_max, double eps, uint32_t check_ever
     uint32_t fin = 0, done = 0;
     int32_t conv = 0;
     uint32_t time = 0;
-    if (check_every == 1 && !c->multi_process && c->snap_buf < 0 && c->kids.empty()) {
+    // (the speculative depth-1 loop is single-process; the dual-residual depth-2 loop also runs one process per slab)
+    if (check_every == 1 && c->snap_buf < 0 && c->kids.empty() && (!c->multi_process || c->variant2)) {
         if ((rc = c->variant2 ? run_every_iteration_t2(c, iter_max, eps, &fin, &conv, &done)
                               : run_every_iteration(c, iter_max, eps, &fin, &conv, &done))) return rc;
         time = iter_max;

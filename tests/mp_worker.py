@@ -124,6 +124,14 @@ def main():
                 sim.init_reference_field()
                 sim.step(nsteps)
                 assert np.array_equal(sim.download_planes(z0, z1 - z0), ref[z0:z1])
+                # the reference's loop, residual examined every iteration (collective): iteration count and field must be the
+                # single domain's whether the run converges on the first or the second update of a depth-2 pass, or not at all
+                for eps, iter_max in ((0.3, 200), (0.28, 200), (0.18, 200), (1e-30, 13)):
+                    To = oracle.init_field(nx, ny, nz)
+                    want = oracle.run(To, D, iter_max, eps)
+                    sim.init_reference_field()
+                    assert sim.run(iter_max, eps, check_every=1) == want, (eps, want)
+                    assert np.array_equal(sim.download_planes(z0, z1 - z0), To[z0:z1]), eps
             dist.barrier()
     dist.barrier()
     dist.destroy_process_group()

@@ -381,8 +381,9 @@ def main():
         traffic = None
         try:
             ent = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(kernel_name)
-            if ent and ent.get("grid") == grid_local:
-                traffic = ent["dram_bytes_per_launch"]      # ncu dram__bytes_read.sum + dram__bytes_write.sum of one launch
+            for e in (ent if isinstance(ent, list) else [ent] if ent else []):
+                if e.get("grid") == grid_local:
+                    traffic = e["dram_bytes_per_launch"]    # ncu dram__bytes_read.sum + dram__bytes_write.sum of one launch
         except Exception:
             pass
         return {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,

@@ -9,7 +9,8 @@ import __graft_entry__ as ge  # noqa: E402
 h3 = ge.load_package()
 n, steps = int(sys.argv[1]), int(sys.argv[2])
 arith = int(sys.argv[3]) if len(sys.argv) > 3 else 0
-with h3.Heat3D(n, n, n, temporal_k=2, arith=arith) as sim:
+shape = tuple(int(v) for v in os.environ["PROF_SHAPE"].split(",")) if os.environ.get("PROF_SHAPE") else (n, n, n)
+with h3.Heat3D(*shape, temporal_k=2, arith=arith) as sim:
     sim.init_reference_field()
     sim.step(steps)
     sim.sync()

@@ -27,9 +27,10 @@
 //   bit 1 (mid plane, level 2): the mid plane is stored split by x parity (even-x cells in one array, odd-x cells in
 //          another), so left / right neighbours are 8-byte words at consecutive lanes - no selects, two 64-bit stores
 //          instead of one 128-bit store per row.
-// Measured (profiles/r02_*): removing the conflicts takes the LSU pipe from 77 % to 56 % but the selects cost issue
-// slots; the kernel is then co-limited by FP64 issue (2 cycles per warp instruction, 208 per thread and plane) and
-// instruction issue, see DESIGN.md.
+// Measured (profiles/r02_*): both bits set remove the conflicts (LSU pipe 77 % -> 56 %) but the selects cost as many issue
+// slots as the wavefronts saved; bit 1 alone is the default ("_P": LSU 66 %, 216 M instead of 260 M instructions per
+// 512^3 launch).  The kernel is then co-limited by FP64 issue (2 cycles per warp instruction, 208 per thread and plane)
+// and instruction issue, see DESIGN.md 3.1b.
 #pragma once
 #include "kernels.cuh"
 
@@ -71,8 +72,6 @@ __device__ __forceinline__ void level_full(const double2 (&c)[RY], const double 
     }
 }
 
-// xy neighbours of a thread's 2 x RY patch, read from a staged (or mid) plane; S points at the thread's first cell.
-// XSW: `swp` lanes (8-15, 24-31) load right-then-left, the others left-then-right, see the header comment.
 // one lane of a converged warp (the PTX way to say "somebody do this once"; lets ptxas keep the TMA issue on the uniform path)
 __device__ __forceinline__ bool elect_one_sync()
 {
@@ -81,6 +80,8 @@ __device__ __forceinline__ bool elect_one_sync()
     return pred != 0;
 }
 
+// xy neighbours of a thread's 2 x RY patch, read from a staged (or mid) plane; S points at the thread's first cell.
+// XSW: `swp` lanes (8-15, 24-31) load right-then-left, the others left-then-right, see the header comment.
 template <int RY, bool XSW>
 __device__ __forceinline__ void load_neighbours(const double* __restrict__ S, int row_pitch, bool swp, double (&xl)[RY], double (&xr)[RY],
                                                 double2& up, double2& dn)

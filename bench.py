@@ -284,7 +284,6 @@ def main():
     n = args.gpus
     if world > 1:
         assert world == n, f"--gpus {n} but WORLD_SIZE={world}"
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")      # stdout carries the one JSON line, nothing else
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     elif n > 1:
         raise SystemExit("for --gpus N>1 launch under torch.distributed.run with one rank per GPU")

@@ -362,7 +362,8 @@ def main():
     barrier()
     wall_ms = (time.perf_counter() - r["t0"]) * 1e3
     clocks = sampler.stop() if rank == 0 else None
-    launches, stencil_launches = r["launches"], r["stencil_launches"]
+    launches, stencil_launches = r["launches"], r["stencil_launches"]      # kernels inside the headline's timed region
+    extra_launches = 0                                                        # ... and inside the additional timed blocks of this line
     dev_ms = max_over_ranks(r["dev_ms"])
     wall_ms = max_over_ranks(wall_ms)
     halo_ms_min = max_over_ranks(r["halo_ms"], dist.ReduceOp.MIN) if world > 1 else r["halo_ms"]
@@ -405,7 +406,7 @@ def main():
             k1_steps = max(3, min(args.steps, 5))
             r1 = timed_steps(s1, tsteps, k1_steps, max(3, min(args.warmup, 3)))
             roofline_k1 = roofline_block(s1.kernel_name(), 1, local_cells, r1["dev_ms"], r1["stencil_launches"], k1_steps, [nx, ny, nz])
-            launches += r1["launches"]
+            extra_launches += r1["launches"]
 
     # N=1: the same kernel in nvcc's FMA contraction of the reference kernel (10 instead of 13 FP64 instructions per update,
     # bit-exact against the oracle's fma ordering, <= 1e-12 from the strict result) - reported beside the strict headline
@@ -417,7 +418,7 @@ def main():
             rf = timed_steps(sf, tsteps, f_steps, max(3, min(args.warmup, 3)))
             arith_fma = {"glups": cells * tsteps * f_steps / (rf["dev_ms"] * 1e-3) / 1e9, "steps": f_steps, "kernel": sf.kernel_name(),
                          "note": "HEAT3D_ARITH_FMA: three fused multiply-adds per update, the contraction nvcc applies to the reference kernel"}
-            launches += rf["launches"]
+            extra_launches += rf["launches"]
 
     # N>1: like-for-like scaling base measured in this run (rank 0 alone on one rank's share), and the strong-scaling block
     scaling_base = parallel_eff = strong = None
@@ -445,7 +446,7 @@ def main():
                 s_ms = max_over_ranks(rs["dev_ms"])
                 s_halo = max_over_ranks(rs["halo_ms"])
                 s_halo_min = max_over_ranks(rs["halo_ms"], dist.ReduceOp.MIN)
-                launches += rs["launches"]
+                extra_launches += rs["launches"]
             sval = scells * ststeps * ssteps / (s_ms * 1e-3) / 1e9
             barrier()
             sbase = max_over_ranks(standalone_rate(h3, sshape, arith, k, local, 125) if rank == 0 else 0.0)
@@ -509,7 +510,7 @@ def main():
                 "config": {"workload": wname, "grid": [nx, ny, nz], "updates_per_step": tsteps, "arith": args.arith, "temporal_k": k,
                            "decomposition": f"{n} z-slab(s), one process per GPU" + (f", ghost planes by {sim.exchange_name()} overlapped with interior compute" if n > 1 else ""),
                            "l2": "inputs exceed L2 (two %.1f GiB buffers per GPU vs 126 MB)" % ((z1 - z0) * ny * nx * 8 / 2**30)},
-                "roofline": roofline, "roofline_k1": roofline_k1, "arith_fma": arith_fma, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+                "roofline": roofline, "roofline_k1": roofline_k1, "arith_fma": arith_fma, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "gpu_launches_other_blocks": int(extra_launches), "clocks": clocks,
                 "parity_preflight": preflight, "scaling_base_glups": scaling_base, "parallel_efficiency": parallel_eff, "strong_1024": strong,
                 "wall_ms_per_step": wall_ms / args.steps, "snapshots": {"count": nsnap, "bytes_each_per_rank": int(snap_buf.nbytes), "stride": ss, "every_steps": args.snapshot_every,
                               "headline": "wall_glups_incl_snapshots"} if snap_buf is not None else None,

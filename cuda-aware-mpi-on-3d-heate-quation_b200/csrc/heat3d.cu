@@ -214,6 +214,7 @@ const std::vector<T2Variant>& t2_variants()
         make_t2<64, 32, 4, 4, 2, 2>("t2_64x32_r4_s4_c2_P"),
         make_t2<64, 32, 4, 4, 2, 0>("t2_64x32_r4_s4_c2_L"),
         make_t2<64, 32, 4, 4, 2, 3>("t2_64x32_r4_s4_c2_X"),
+        make_t2<64, 32, 4, 4, 2, 6>("t2_64x32_r4_s4_c2_Q"),      // "_P" with neighbour-to-neighbour barriers instead of the CTA barrier
         make_t2<64, 16, 2, 4, 3, 2>("t2_64x16_r2_s4_c3_P"),
         // 512 threads, one CTA per SM: smaller redundant level-1 ring (124x30 / 60x62 of 128x32 / 64x64 useful); measured
         // slower than two independent 256-thread CTAs per SM (one barrier domain of 16 warps), kept for experiments

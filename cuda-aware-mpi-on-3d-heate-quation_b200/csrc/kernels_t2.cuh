@@ -43,7 +43,7 @@ struct Tma2Cfg {
     static constexpr int ROWS = CY + 2;
     static constexpr int STAGE_BYTES = ROW * ROWS * 8;
     static constexpr int STAGE_STRIDE = (STAGE_BYTES + 127) / 128 * 128;
-    static constexpr int SMEM_BYTES = (STAGES + 2) * STAGE_STRIDE + STAGES * 8;   // stages | 2 mid planes | full barriers
+    static constexpr int SMEM_BYTES = (STAGES + 2) * STAGE_STRIDE + 2 * STAGES * 8;   // stages | 2 mid planes | full barriers | empty barriers
 };
 
 // Per-thread constants of the two levels.
@@ -78,6 +78,12 @@ __device__ __forceinline__ bool elect_one_sync()
     uint32_t pred;
     asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(pred));
     return pred != 0;
+}
+
+// named barrier 2 + pair between the two warps `pair` and `pair + 1`
+__device__ __forceinline__ void pair_barrier(int pair)
+{
+    asm volatile("bar.sync %0, 64;" ::"r"(2 + pair) : "memory");
 }
 
 // xy neighbours of a thread's 2 x RY patch, read from a staged (or mid) plane; S points at the thread's first cell.
@@ -136,6 +142,9 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     extern __shared__ __align__(128) unsigned char smem[];
     unsigned char* mid = smem + STAGES * Cfg::STAGE_STRIDE;
     uint64_t* full = (uint64_t*)(smem + (STAGES + 2) * Cfg::STAGE_STRIDE);
+    uint64_t* empty = full + STAGES;                            // PSYNC only
+    constexpr bool PSYNC = (XMODE & 4) != 0;                    // neighbour-to-neighbour barriers instead of one CTA barrier per plane
+    static_assert(!PSYNC || NWARP <= 14, "one named barrier per pair of neighbouring warps");
 
     const int tid = threadIdx.x;
     const int ntiles = w.ntx * w.nty;
@@ -151,7 +160,10 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
 
     if (tid == 0) {
 #pragma unroll
-        for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            if (PSYNC) mbar_init(&empty[s], NWARP);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 #pragma unroll
@@ -217,15 +229,29 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
 #pragma unroll
     for (int r = 0; r < RY; ++r) C0[0][r] = C0[1][r] = C0[2][r] = C1[0][r] = C1[1][r] = C1[2][r] = make_double2(0.0, 0.0);
 
-    // The per-plane CTA barrier is a named barrier (id 1) so that warps with nothing to compute can take part in it from
-    // a loop of their own instead of dragging a predicate through the compute loop.
-    auto plane_barrier = [] { asm volatile("bar.sync 1, %0;" ::"n"(NTHR) : "memory"); };
-    // after the barrier of iteration q: plane q-1's stage is free, refill it with plane q-1+STAGES.  The duty rotates over
-    // the warps; `warp` is a warp-uniform value and the issuing lane is elected, so the seven warps whose turn it is not
-    // pay one uniform compare-and-branch.
+    // End of a plane.  Default: one CTA barrier (named, id 1, so that warps with nothing to compute can take part in it from
+    // a loop of their own): afterwards plane q-1's stage has been read by everyone and this iteration's mid plane is complete.
+    // PSYNC: nobody but a warp's two neighbours in y reads its rows of the mid plane (its x neighbours are its own lanes), so
+    // each warp meets only them (named barriers 2.., one per pair, 64 threads each; lower neighbour first, which cannot
+    // deadlock: every barrier is the first one for its upper warp), and the stage is handed back through an `empty` mbarrier
+    // with one arrival per warp, which the refilling lane waits on.  Warps then drift apart by at most one plane per neighbour.
+    auto end_of_plane = [&](int q, uint32_t sprev) {
+        if (PSYNC) {
+            __syncwarp();
+            if (q >= 1 && lane == 0) mbar_arrive(&empty[sprev]);
+            if (warp > 0) pair_barrier(warp - 1);
+            if (warp < NWARP - 1) pair_barrier(warp);
+        } else {
+            asm volatile("bar.sync 1, %0;" ::"n"(NTHR) : "memory");
+        }
+    };
+    // after that: plane q-1's stage is free, refill it with plane q-1+STAGES.  The duty rotates over the warps; `warp` is a
+    // warp-uniform value and the issuing lane is elected, so the seven warps whose turn it is not pay one uniform
+    // compare-and-branch.
     auto refill = [&](int q, uint32_t sprev) {
         if (warp == (q & (NWARP - 1)) && q >= 1 && q - 1 + STAGES < niter) {
             if (elect_one_sync()) {
+                if (PSYNC) mbar_wait(&empty[sprev], (uint32_t)(((q - 1) / STAGES) & 1));
                 mbar_arrive_expect_tx(&full[sprev], Cfg::STAGE_BYTES);
                 tma_load_3d(smem + sprev * Cfg::STAGE_STRIDE, &tmap, &full[sprev], bx, by, zs - 2 + q - 1 + STAGES);
             }
@@ -308,7 +334,7 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
                     out += g.plane;
                     if (MIRROR) { if (mir) mir += g.plane; ++zout; }
                 }
-                plane_barrier();        // plane q-1's stage has been read by everyone; this iteration's mid plane is complete
+                end_of_plane(q, sprev);
                 refill(q, sprev);
                 if (++s == STAGES) { s = 0; ph ^= 1u; }
                 par ^= 1;
@@ -334,7 +360,7 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
     if (!active) {      // nothing to compute: keep the barriers and take the refill turns
         uint32_t s = 0;
         for (int q = 0; q < niter; ++q) {
-            plane_barrier();
+            end_of_plane(q, s == 0 ? STAGES - 1 : s - 1);
             refill(q, s == 0 ? STAGES - 1 : s - 1);
             if (++s == STAGES) s = 0;
         }

@@ -10,8 +10,9 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 # cx,cy,rows/thread,stages,CTAs/SM,chunk_len,xmode  (shared-memory access mode, kernels_t2.cuh: 0 "_L" plain loads,
-# 1 "_S" swapped x-neighbour loads, 2 "_P" parity-split mid plane, 3 "_X" both)
-T2_TUNES = ["64,32,4,4,2,7,2", "64,32,4,4,2,7,0", "64,32,4,4,2,7,3", "64,16,2,4,3,7,2", "128,32,4,4,1,7,2", "64,64,4,4,1,7,2"]
+# 2 "_P" parity-split mid plane, 3 "_X" that + swapped x-neighbour loads from the stage, 6 "_Q" = "_P" with
+# neighbour-to-neighbour barriers)
+T2_TUNES = ["64,32,4,4,2,7,2", "64,32,4,4,2,7,0", "64,32,4,4,2,7,3", "64,32,4,4,2,7,6", "64,16,2,4,3,7,2", "128,32,4,4,1,7,2", "64,64,4,4,1,7,2"]
 
 
 @pytest.fixture(scope="module")
@@ -55,7 +56,7 @@ def test_every_depth2_variant(h3, oracle, tune):
     ref = _oracle_field(oracle, nx, ny, nz, nsteps)
     prev = _oracle_field(oracle, nx, ny, nz, nsteps - 1)
     with h3.Heat3D(nx, ny, nz, temporal_k=2) as sim:
-        assert sim.kernel_name() == "t2_%sx%s_r%s_s%s_c%s" % tuple(f[:5]) + {"0": "_L", "1": "_S", "2": "_P", "3": "_X"}[f[6]]
+        assert sim.kernel_name() == "t2_%sx%s_r%s_s%s_c%s" % tuple(f[:5]) + {"0": "_L", "2": "_P", "3": "_X", "6": "_Q"}[f[6]]
         sim.init_reference_field()
         res = sim.step_residual(nsteps)               # even count: the residual comes out of the depth-2 kernel
         got = sim.download()

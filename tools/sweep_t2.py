@@ -27,7 +27,7 @@ cells = (shape[0] - 2) * (shape[1] - 2) * (shape[2] - 2)
 for arith in ((0,) if os.environ.get("SWEEP_STRICT_ONLY") else (0, 1)):
     for tune in TUNES:
         for ch in CHUNKS:
-            base, xmode = tune[:-1], "LSPX".index(tune[-1])
+            base, xmode = tune[:-1], {"L": 0, "S": 1, "P": 2, "X": 3, "Q": 6}[tune[-1]]
             os.environ["HEAT3D_T2_TUNE"] = f"{base},{ch},{xmode}"
             try:
                 with h3.Heat3D(*shape, arith=arith, temporal_k=2) as sim:

@@ -178,8 +178,15 @@ def bind_to_gpu_numa_node(index):
         if bus.startswith("0000"):
             bus = bus[4:]                                  # nvidia-smi prints an 8-digit domain, sysfs a 4-digit one
         node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        how = "from sysfs"
         if node < 0:
-            return "numa node unknown"
+            # the platform does not say (virtualised PCI topology): spread the ranks evenly over the host's NUMA nodes in
+            # device order, which is how 8-GPU boards are wired (GPUs 0-3 on one socket, 4-7 on the other)
+            nodes = sorted(int(d[4:]) for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit())
+            ngpu = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")))
+            if len(nodes) < 2 or ngpu < 2:
+                return f"numa node unknown, {len(nodes)} host node(s): unbound"
+            node, how = nodes[min(len(nodes) - 1, index * len(nodes) // ngpu)], f"guessed, {len(nodes)} host nodes"
         cpus = set()
         for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
             lo, _, hi = part.partition("-")
@@ -188,7 +195,7 @@ def bind_to_gpu_numa_node(index):
         if not cpus:
             return f"numa node {node}: no allowed CPUs"
         os.sched_setaffinity(0, cpus)
-        return f"numa node {node}, {len(cpus)} CPUs"
+        return f"numa node {node} ({how}), {len(cpus)} CPUs"
     except Exception as e:      # no sysfs entry, no nvidia-smi, ...: run unbound
         return f"unbound ({type(e).__name__})"
 

@@ -29,7 +29,8 @@
  * available (either way `nccl_unique_id` is required: NCCL carries the bootstrap and the scalar reductions).
  * In a multi-process run heat3d_create, heat3d_init_reference_field, heat3d_upload*, heat3d_step_residual,
  * heat3d_run, heat3d_mean_abs_error_vs_y and heat3d_destroy are collective: every process calls them, in the
- * same order.  nslabs = nlocal = 1 is the plain single-GPU case.
+ * same order.  nslabs = nlocal = 1 is the plain single-GPU case.  `nslabs_y` > 1 adds a cut along y (row ranges x z-slabs, one
+ * process): see heat3d_params.
  */
 #ifndef HEAT3D_H
 #define HEAT3D_H
@@ -169,7 +170,8 @@ int heat3d_step_residual(heat3d_ctx* ctx, uint32_t nsteps, double* residual);
  * (check_every = 1 reproduces the reference's iteration count exactly, and the field is then the state after
  * exactly that iteration).  With check_every = 1 the GPU is not left waiting for the host's check: on a depth-1
  * context the next iteration is queued ahead and dropped again if it turns out not to be needed; on a depth-2
- * context one pass yields the residuals of both its iterations.  *final_iters receives the reference's
+ * context one pass yields the residuals of both its iterations (also one process per slab: a single 3-double all-reduce per pass
+ * gives every process both values).  *final_iters receives the reference's
  * finalNumIterations (0-based index of the converging iteration, cu:1070-1073; 0 if not converged), *converged its
  * globalBreakCondition, *applied (optional) the number of updates performed. */
 int heat3d_run(heat3d_ctx* ctx, uint32_t iter_max, double eps, uint32_t check_every,

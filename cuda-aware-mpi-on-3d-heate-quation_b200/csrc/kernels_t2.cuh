@@ -327,9 +327,18 @@ __global__ void __launch_bounds__((CX / 2) * (CY / RY), MINB)
                         for (int r = 0; r < RY; ++r)
                             store_pair(out + (long long)r * g.pitch, mnow ? mnow + (long long)r * g.pitch : nullptr, o[r], pl.st, r);
                     }
-                    if (RES) {
+                    if (RES) {      // residual of the second update over the cells this thread stores (same warp-uniform split)
+                        if (warp_pairs) {
     #pragma unroll
-                        for (int r = 0; r < RY; ++r) res_pair(rmax, o[r], c1p1[r], pl.st, r);
+                            for (int r = 0; r < RY; ++r)
+                                if ((pair_rows >> r) & 1u) {
+                                    res_track(rmax, o[r].x, c1p1[r].x);
+                                    res_track(rmax, o[r].y, c1p1[r].y);
+                                }
+                        } else {
+    #pragma unroll
+                            for (int r = 0; r < RY; ++r) res_pair(rmax, o[r], c1p1[r], pl.st, r);
+                        }
                     }
                     out += g.plane;
                     if (MIRROR) { if (mir) mir += g.plane; ++zout; }

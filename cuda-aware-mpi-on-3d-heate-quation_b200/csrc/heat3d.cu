@@ -479,7 +479,7 @@ long long plan_chunks(h3::TmaWork& w, int za, int zb, int ends, int end_len, int
         const long long key = ((long long)nzp << 8) | (long long)(w.n_end << 4) | (end_len & 15);
         auto it = s.plan_cache.find(key);
         if (it == s.plan_cache.end()) {
-            static const double ovh = getenv("HEAT3D_T2_OVH") ? atof(getenv("HEAT3D_T2_OVH")) : 6.0;
+            static const double ovh = getenv("HEAT3D_T2_OVH") ? atof(getenv("HEAT3D_T2_OVH")) : 3.0;
             static const int max_len = getenv("HEAT3D_T2_MAXLEN") ? atoi(getenv("HEAT3D_T2_MAXLEN")) : 160;
             const ChunkSplit cs = plan_guided(nzp, ntiles, slots, ntiles * w.n_end, end_len + ovh, ovh, max_len);
             it = s.plan_cache.emplace(key, std::array<int, 4>{cs.len, cs.n_long, cs.len2, cs.split}).first;
